@@ -1,0 +1,159 @@
+/*
+ * pdgpu.h -- C ABI of libpdgpu.so, the B200 (sm_100a) pangenome-graph engine.
+ *
+ * This is the drop-in boundary for prairiedog's graph-construction hot path.  The reference has
+ * no FFI of its own on this path except LemonGraph's cffi module; every entry point below names
+ * the reference interface it replaces (paths relative to the reference checkout):
+ *
+ *   prairiedog/kmers.py:51-150          Kmers._load / next / _count_unique
+ *   prairiedog/subgraph_ref.py:39-115   SubgraphRef.update_graph
+ *   prairiedog/lemon_graph.py:99-334    LGGraph.upsert_node / add_edge / save / nodes / edges /
+ *                                       connected / _find_path / path
+ *   lemongraph/LemonGraph/cffi_stubs.py:100-236   graph_node_resolve / graph_edge_resolve /
+ *                                       graph_txn_* / graph_nodes / graph_edges (native boundary)
+ *
+ * Conventions: plain C, no torch types.  Every function returns 0 on success and a negative
+ * PDG_E_* code on failure; pdg_last_error() then describes the failure (thread local).  A graph
+ * handle is used by one host thread at a time.  Pointers named d_* are device pointers (for
+ * example torch.Tensor.data_ptr()), h_* are host pointers.  All work is enqueued on the stream
+ * given to pdg_set_stream (default: the legacy default stream) and calls that return data to
+ * the host synchronise that stream before returning.  There is no CPU implementation behind any
+ * of these calls.
+ *
+ * Encoding: a k-mer over {A,T,C,G} is the integer sum(base[j] << 2*(k-1-j)) with A=0,T=1,C=2,G=3
+ * (the enumeration order of kmers.py:17-24 possible_kmers), k <= 31.  Codes with bit 63 set are
+ * opaque node keys interned by the host (node values that are not clean k-mers, for example the
+ * three letter names of tests/test_connected.py).  edge_value is a signed 32-bit integer.
+ */
+#ifndef PDGPU_H
+#define PDGPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PDG_ABI_VERSION 1
+
+#define PDG_OK            0
+#define PDG_E_INVALID    -1   /* bad argument / bad state */
+#define PDG_E_CUDA       -2   /* a CUDA runtime call or kernel failed */
+#define PDG_E_CAPACITY   -3   /* caller-provided buffer too small (required size reported) */
+#define PDG_E_NOMEM      -4   /* device allocation failed */
+#define PDG_E_COMM       -5   /* NCCL failure */
+
+typedef struct pdg_graph pdg_graph;
+
+/* result of pdg_ingest_fasta */
+typedef struct pdg_ingest_info {
+    uint64_t n_bytes;        /* bytes parsed */
+    uint64_t n_headers;      /* lines starting with '>' (kmers.py:64-71) */
+    uint64_t n_residues;     /* sequence characters after rstrip (kmers.py:63,72-73) */
+    uint64_t n_dirty;        /* sequence bytes outside [ACGT] + interior blanks + bare CR */
+    uint64_t residue_base;   /* index of the first residue of this file in the genome store */
+    uint64_t appended;       /* 1 if residues were appended (n_dirty == 0), else 0 */
+} pdg_ingest_info;
+
+/* one path-query hit: a occurs as the source of edge (type_id, i), b as the target of edge
+ * (type_id, j), i <= j, j - i <= max_len  (lemon_graph.py:275-334, graph.py:82-113) */
+typedef struct pdg_hit {
+    uint32_t type_id;
+    int32_t  i;
+    int32_t  j;
+    uint32_t src_tgt_id;     /* node id of the target of the start edge */
+} pdg_hit;
+
+/* counters of the last pdg_finalize, for roofline accounting (bench.py) */
+typedef struct pdg_build_stats {
+    uint64_t n_residues, n_contigs, n_kmers, n_edge_records, n_nodes, n_edges;
+    uint64_t node_path;      /* 0 = presence bitmap, 1 = radix sort + run-length compaction */
+    uint64_t general_sort;   /* 0 = fast path (records arrive sorted by (type,value)), 1 = full key */
+    uint64_t sort_passes_csr, sort_passes_csc;
+    float ms_nodes, ms_records, ms_sort_csr, ms_sort_csc, ms_pack_csr, ms_pack_csc, ms_total;
+    float ms_onesweep_avg;   /* average duration of one onesweep pass kernel */
+    uint64_t onesweep_launches, onesweep_records;
+} pdg_build_stats;
+
+const char *pdg_last_error(void);
+int pdg_abi_version(void);
+
+/* lifetime.  Replaces LGGraph.__init__ / clear (lemon_graph.py:27-42,130-131). */
+pdg_graph *pdg_create(int device, int k);
+void pdg_destroy(pdg_graph *g);
+int pdg_set_stream(pdg_graph *g, void *cuda_stream);
+int pdg_clear(pdg_graph *g);
+
+/* K0+K1a: parse one FASTA file image that is resident on the device and append its residues,
+ * packed to 2 bits, to the genome store.  Replaces Kmers._load (kmers.py:51-77).
+ * h_header_table receives n_headers rows of {byte_begin, byte_end, residue_index}: the header
+ * line is bytes [byte_begin, byte_end) of the file and residue_index residues precede it.
+ * If n_headers > cap_headers the call fails with PDG_E_CAPACITY and info->n_headers holds the
+ * required capacity.  If n_dirty != 0 nothing is appended (the host must route the file through
+ * pdg_add_edges_host). */
+int pdg_ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes,
+                     uint64_t *h_header_table, uint64_t cap_headers, pdg_ingest_info *info);
+
+/* Declares contigs over residues already in the store: contig c covers residues
+ * [h_begin[c], h_begin[c]+h_len[c]) and all its edges carry type id h_type_id[c].  Contigs with
+ * h_len <= k yield nothing (kmers.py:110-117).  Replaces the per-contig bookkeeping of
+ * SubgraphRef.update_graph (subgraph_ref.py:51-102). */
+int pdg_add_contigs(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len,
+                    const uint32_t *h_type_id, uint64_t n_contigs);
+
+/* Kmers.__len__ / unique_kmers (kmers.py:48-49,134-150) for a set of contigs in the store. */
+int pdg_kmer_stats(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len,
+                   uint64_t n_contigs, uint64_t *n_kmers, uint64_t *n_unique);
+
+/* k-mer codes of one contig (device output, n = len-k+1 codes); Kmers.next as a bulk call. */
+int pdg_emit_codes(pdg_graph *g, uint64_t begin, uint64_t len, uint64_t *d_codes_out);
+
+/* Per-edge compatibility path: LGGraph.add_edge / upsert_node (lemon_graph.py:99-128) and
+ * graph_edge_resolve / graph_node_resolve (cffi_stubs.py).  Host arrays are copied. */
+int pdg_add_edges_host(pdg_graph *g, const uint64_t *h_src_code, const uint64_t *h_tgt_code,
+                       const uint32_t *h_type_id, const int32_t *h_value, uint64_t n);
+int pdg_add_nodes_host(pdg_graph *g, const uint64_t *h_code, uint64_t n);
+
+/* K2+K3: node dedup -> dense ids, edge dedup -> CSR + CSC.  Replaces the LMDB upserts behind
+ * LGGraph.add_edge + LGGraph.save (lemon_graph.py:115-128,154-157; lemongraph.c:661-685).
+ * flags: bit0 = force the radix-sort node path, bit1 = force the full-key edge sort. */
+#define PDG_F_FORCE_SORT_NODES 1
+#define PDG_F_FORCE_GENERAL    2
+int pdg_finalize(pdg_graph *g, int flags);
+int pdg_counts(pdg_graph *g, uint64_t *n_nodes, uint64_t *n_edges, uint64_t *n_kmers);
+int pdg_get_build_stats(pdg_graph *g, pdg_build_stats *out);
+
+/* LGGraph.nodes / edges (lemon_graph.py:133-149).  Outputs are HOST arrays sized from
+ * pdg_counts.  Nodes come in ascending code order (id = index); edges in CSR order, i.e. sorted by
+ * (src id, type id, value, tgt id).  Any output pointer may be NULL. */
+int pdg_export_nodes(pdg_graph *g, uint64_t *h_codes);
+int pdg_export_edges(pdg_graph *g, uint32_t *h_src_id, uint32_t *h_tgt_id, uint32_t *h_type_id,
+                     int32_t *h_value);
+/* order-independent 64-bit checksums of the canonical node set and edge set (sum of a mixed
+ * hash over (code) / (src code, tgt code, type, value)), computed on the device */
+int pdg_checksum(pdg_graph *g, uint64_t *nodes_sum, uint64_t *edges_sum);
+
+/* K4: batched queries.  h_a/h_b are node codes.  pdg_query_connected replaces LGGraph.connected
+ * (lemon_graph.py:178-219): per query the number of start edges.  pdg_query_paths replaces
+ * LGGraph.path (lemon_graph.py:275-334): hits per query with j - i <= max_len.  Results stay in
+ * graph-owned device memory until the next query call; pdg_query_fetch copies them to the host
+ * (h_offsets has n_q + 1 entries).  pdg_query_walk materialises the node ids of one hit's path
+ * (_find_path, lemon_graph.py:221-273): n = j - i + 2 ids; status 0 ok, 1 broken, 2 ambiguous. */
+int pdg_query_connected(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q,
+                        uint64_t *total_starts);
+int pdg_query_paths(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q,
+                    int64_t max_len, uint64_t *total_hits);
+int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits);
+int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint32_t *h_node_ids,
+                   int32_t *status);
+
+/* K5: multi-GPU (one process per GPU).  The host exchanges the 128-byte id with
+ * torch.distributed; records are hash partitioned with one grouped ncclSend/ncclRecv exchange
+ * inside pdg_finalize.  No reference counterpart. */
+int pdg_comm_unique_id(uint8_t *h_id128);
+int pdg_comm_init(pdg_graph *g, const uint8_t *h_id128, int rank, int world);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDGPU_H */
