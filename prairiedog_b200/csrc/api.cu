@@ -1,0 +1,273 @@
+// api.cu -- the extern "C" surface declared in include/pdgpu.h.
+#include "common.cuh"
+#include <stdarg.h>
+#include <string.h>
+#include <new>
+
+namespace pdg {
+static thread_local char g_err[1024] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+}  // namespace pdg
+
+using namespace pdg;
+
+#define PDG_API_BEGIN                                   \
+    if (!g) {                                           \
+        set_error("null graph handle");                 \
+        return PDG_E_INVALID;                           \
+    }                                                   \
+    try {                                               \
+        if (cudaSetDevice(g->device) != cudaSuccess) {  \
+            set_error("cudaSetDevice(%d) failed", g->device); \
+            return PDG_E_CUDA;                          \
+        }
+#define PDG_API_END                                     \
+    }                                                   \
+    catch (const pdg::CudaError &e) { return e.code; }  \
+    catch (const std::bad_alloc &) {                    \
+        set_error("host allocation failed");            \
+        return PDG_E_NOMEM;                             \
+    }
+
+extern "C" {
+
+const char *pdg_last_error(void) { return g_err; }
+int pdg_abi_version(void) { return PDG_ABI_VERSION; }
+
+pdg_graph *pdg_create(int device, int k) {
+    if (k < 1 || k > 31) {
+        set_error("pdg_create: k=%d outside [1,31]", k);
+        return nullptr;
+    }
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) {
+        set_error("pdg_create: CUDA device %d not available (%d devices) -- there is no CPU path", device, n);
+        return nullptr;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) {
+        set_error("pdg_create: cudaSetDevice(%d) failed", device);
+        return nullptr;
+    }
+    pdg_graph *g = new (std::nothrow) pdg_graph();
+    if (!g) return nullptr;
+    g->device = device;
+    g->k = k;
+    return g;
+}
+
+void pdg_destroy(pdg_graph *g) {
+    if (!g) return;
+    cudaSetDevice(g->device);
+    cudaStreamSynchronize(g->stream);
+    delete g;
+}
+
+int pdg_set_stream(pdg_graph *g, void *cuda_stream) {
+    PDG_API_BEGIN
+    g->stream = reinterpret_cast<cudaStream_t>(cuda_stream);
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_clear(pdg_graph *g) {
+    PDG_API_BEGIN
+    PDG_CUDA(cudaStreamSynchronize(g->stream));
+    g->n_res = 0;
+    if (g->packed.p) PDG_CUDA(cudaMemsetAsync(g->packed.p, 0, g->packed.cap, g->stream));
+    g->c_begin.clear(); g->c_len.clear(); g->c_edge_base.clear(); g->c_type.clear();
+    g->n_kmers = g->n_gen_edges = 0;
+    g->contigs_sorted_fresh = true;
+    g->x_src.clear(); g->x_tgt.clear(); g->x_nodes.clear(); g->x_type.clear(); g->x_val.clear();
+    g->finalized = false;
+    g->n_nodes = g->n_edges = 0;
+    g->q_n = g->q_total = 0;
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes, uint64_t *h_header_table,
+                     uint64_t cap_headers, pdg_ingest_info *info) {
+    PDG_API_BEGIN
+    if (!info || (n_bytes && !d_bytes)) {
+        set_error("pdg_ingest_fasta: null argument");
+        return PDG_E_INVALID;
+    }
+    return ingest_fasta(g, d_bytes, n_bytes, h_header_table, cap_headers, info);
+    PDG_API_END
+}
+
+int pdg_add_contigs(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len, const uint32_t *h_type_id,
+                    uint64_t n_contigs) {
+    PDG_API_BEGIN
+    const uint64_t k = (uint64_t)g->k;
+    for (uint64_t i = 0; i < n_contigs; ++i) {
+        if (h_begin[i] + h_len[i] > g->n_res) {
+            set_error("pdg_add_contigs: contig %llu [%llu,+%llu) beyond the %llu residues in the store",
+                      (unsigned long long)i, (unsigned long long)h_begin[i], (unsigned long long)h_len[i],
+                      (unsigned long long)g->n_res);
+            return PDG_E_INVALID;
+        }
+        if (h_len[i] <= k) continue;   // kmers.py:110-117: a contig with len <= k yields nothing
+        if (!g->c_begin.empty() && h_begin[i] < g->c_begin.back() + g->c_len.back()) {
+            set_error("pdg_add_contigs: contigs must be ascending and disjoint");
+            return PDG_E_INVALID;
+        }
+        if (!g->c_type.empty()) {
+            uint32_t mx = 0;
+            // strictly increasing type ids keep the generated records sorted by (type, value)
+            mx = g->c_type.back();
+            if (h_type_id[i] <= mx) g->contigs_sorted_fresh = false;
+        }
+        g->c_begin.push_back(h_begin[i]);
+        g->c_len.push_back(h_len[i]);
+        g->c_type.push_back(h_type_id[i]);
+        g->c_edge_base.push_back(g->n_gen_edges);
+        g->n_gen_edges += h_len[i] - k;
+        g->n_kmers += h_len[i] - k + 1;
+    }
+    g->finalized = false;
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_kmer_stats(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len, uint64_t n_contigs,
+                   uint64_t *n_kmers, uint64_t *n_unique) {
+    PDG_API_BEGIN
+    return kmer_stats(g, h_begin, h_len, n_contigs, n_kmers, n_unique);
+    PDG_API_END
+}
+
+int pdg_emit_codes(pdg_graph *g, uint64_t begin, uint64_t len, uint64_t *d_codes_out) {
+    PDG_API_BEGIN
+    return emit_codes(g, begin, len, d_codes_out);
+    PDG_API_END
+}
+
+int pdg_add_edges_host(pdg_graph *g, const uint64_t *h_src_code, const uint64_t *h_tgt_code,
+                       const uint32_t *h_type_id, const int32_t *h_value, uint64_t n) {
+    PDG_API_BEGIN
+    g->x_src.insert(g->x_src.end(), h_src_code, h_src_code + n);
+    g->x_tgt.insert(g->x_tgt.end(), h_tgt_code, h_tgt_code + n);
+    g->x_type.insert(g->x_type.end(), h_type_id, h_type_id + n);
+    g->x_val.insert(g->x_val.end(), h_value, h_value + n);
+    g->finalized = false;
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_add_nodes_host(pdg_graph *g, const uint64_t *h_code, uint64_t n) {
+    PDG_API_BEGIN
+    g->x_nodes.insert(g->x_nodes.end(), h_code, h_code + n);
+    g->finalized = false;
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_finalize(pdg_graph *g, int flags) {
+    PDG_API_BEGIN
+    return finalize(g, flags);
+    PDG_API_END
+}
+
+int pdg_counts(pdg_graph *g, uint64_t *n_nodes, uint64_t *n_edges, uint64_t *n_kmers) {
+    PDG_API_BEGIN
+    if (n_nodes) *n_nodes = g->n_nodes;
+    if (n_edges) *n_edges = g->n_edges;
+    if (n_kmers) *n_kmers = g->n_kmers;
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_get_build_stats(pdg_graph *g, pdg_build_stats *out) {
+    PDG_API_BEGIN
+    *out = g->stats;
+    return PDG_OK;
+    PDG_API_END
+}
+
+static int need_final(pdg_graph *g, const char *who) {
+    if (!g->finalized) {
+        set_error("%s before pdg_finalize", who);
+        return PDG_E_INVALID;
+    }
+    return PDG_OK;
+}
+
+int pdg_export_nodes(pdg_graph *g, uint64_t *h_codes) {
+    PDG_API_BEGIN
+    if (need_final(g, "pdg_export_nodes")) return PDG_E_INVALID;
+    if (h_codes && g->n_nodes)
+        PDG_CUDA(cudaMemcpyAsync(h_codes, g->node_codes.p, g->n_nodes * 8, cudaMemcpyDeviceToHost, g->stream));
+    PDG_CUDA(cudaStreamSynchronize(g->stream));
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_export_edges(pdg_graph *g, uint32_t *h_src_id, uint32_t *h_tgt_id, uint32_t *h_type_id, int32_t *h_value) {
+    PDG_API_BEGIN
+    if (need_final(g, "pdg_export_edges")) return PDG_E_INVALID;
+    cudaStream_t s = g->stream;
+    const uint64_t ne = g->n_edges, nn = g->n_nodes;
+    if (ne == 0) return PDG_OK;
+    if (h_tgt_id) PDG_CUDA(cudaMemcpyAsync(h_tgt_id, g->csr_tgt.p, ne * 4, cudaMemcpyDeviceToHost, s));
+    if (h_type_id) PDG_CUDA(cudaMemcpyAsync(h_type_id, g->csr_type.p, ne * 4, cudaMemcpyDeviceToHost, s));
+    if (h_value) PDG_CUDA(cudaMemcpyAsync(h_value, g->csr_val.p, ne * 4, cudaMemcpyDeviceToHost, s));
+    std::vector<uint64_t> rp;
+    if (h_src_id) {
+        rp.resize(nn + 1);
+        PDG_CUDA(cudaMemcpyAsync(rp.data(), g->row_ptr.p, (nn + 1) * 8, cudaMemcpyDeviceToHost, s));
+    }
+    PDG_CUDA(cudaStreamSynchronize(s));
+    if (h_value)
+        for (uint64_t e = 0; e < ne; ++e) h_value[e] = (int32_t)((uint32_t)h_value[e] ^ 0x80000000u);
+    if (h_src_id)
+        for (uint64_t v = 0; v < nn; ++v)
+            for (uint64_t e = rp[v]; e < rp[v + 1]; ++e) h_src_id[e] = (uint32_t)v;
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_checksum(pdg_graph *g, uint64_t *nodes_sum, uint64_t *edges_sum) {
+    PDG_API_BEGIN
+    if (need_final(g, "pdg_checksum")) return PDG_E_INVALID;
+    return checksum(g, nodes_sum, edges_sum);
+    PDG_API_END
+}
+
+int pdg_query_connected(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q,
+                        uint64_t *total_starts) {
+    PDG_API_BEGIN
+    return query_run(g, h_a, h_b, n_q, -1, true, total_starts);
+    PDG_API_END
+}
+
+int pdg_query_paths(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q, int64_t max_len,
+                    uint64_t *total_hits) {
+    PDG_API_BEGIN
+    return query_run(g, h_a, h_b, n_q, max_len, false, total_hits);
+    PDG_API_END
+}
+
+int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits) {
+    PDG_API_BEGIN
+    cudaStream_t s = g->stream;
+    if (h_offsets) PDG_CUDA(cudaMemcpyAsync(h_offsets, g->q_off.p, (g->q_n + 1) * 8, cudaMemcpyDeviceToHost, s));
+    if (h_hits && g->q_total)
+        PDG_CUDA(cudaMemcpyAsync(h_hits, g->q_hits.p, g->q_total * sizeof(pdg_hit), cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint32_t *h_node_ids, int32_t *status) {
+    PDG_API_BEGIN
+    return query_walk(g, src_code, hit, h_node_ids, status);
+    PDG_API_END
+}
+
+}  // extern "C"

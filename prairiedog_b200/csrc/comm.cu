@@ -1,0 +1,255 @@
+// comm.cu -- K5: multi-GPU node deduplication (one process per GPU, NCCL over NVLink/NVSwitch).
+//
+// The reference has no distributed path at all: every Snakemake job writes into
+// one LMDB file behind a single-writer lock.  Here genomes shard by sample: every rank keeps the
+// edges of its own genomes (an edge is unique on (type,value) and a type belongs to one genome,
+// so edges never need to move), and only k-mer NODE keys are exchanged:
+//   1. each rank deduplicates its own k-mer codes                         (bitmap / sort+RLE)
+//   2. codes are hash partitioned, owner(code) = mix64(code) % world, and exchanged with ONE
+//      grouped ncclSend/ncclRecv all-to-all (counts first, W x W uint64 ncclAllGather)
+//   3. each owner radix-sorts + run-length compacts what it received   -> its owned unique set
+//   4. the owned sets (disjoint) are all-gathered and sorted -> the same global node table,
+//      hence the same dense node ids, on every rank.
+// NCCL is resolved with dlopen("libnccl.so.2") so that the library has no link-time dependency
+// on it and picks up the copy torch already loaded.
+#include "common.cuh"
+#include <dlfcn.h>
+#include <nccl.h>
+#include <algorithm>
+
+namespace pdg {
+
+struct NcclApi {
+    void *h = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+static NcclApi *nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        api.h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!api.h) api.h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (api.h) {
+#define PDG_SYM(field, name) api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.h, name))
+            PDG_SYM(GetUniqueId, "ncclGetUniqueId");
+            PDG_SYM(CommInitRank, "ncclCommInitRank");
+            PDG_SYM(CommDestroy, "ncclCommDestroy");
+            PDG_SYM(AllGather, "ncclAllGather");
+            PDG_SYM(Broadcast, "ncclBroadcast");
+            PDG_SYM(Send, "ncclSend");
+            PDG_SYM(Recv, "ncclRecv");
+            PDG_SYM(GroupStart, "ncclGroupStart");
+            PDG_SYM(GroupEnd, "ncclGroupEnd");
+            PDG_SYM(GetErrorString, "ncclGetErrorString");
+#undef PDG_SYM
+        }
+    }
+    if (!api.h || !api.GetUniqueId || !api.CommInitRank || !api.AllGather || !api.Broadcast || !api.Send ||
+        !api.Recv || !api.GroupStart || !api.GroupEnd) {
+        set_error("libnccl.so.2 could not be loaded: %s", dlerror());
+        return nullptr;
+    }
+    return &api;
+}
+
+struct CommError { int code; };
+#define PDG_NCCL(api, expr)                                                                   \
+    do {                                                                                      \
+        ncclResult_t _r = (expr);                                                             \
+        if (_r != ncclSuccess) {                                                              \
+            set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,                           \
+                      (api)->GetErrorString ? (api)->GetErrorString(_r) : "nccl error");     \
+            throw pdg::CudaError{PDG_E_COMM};                                                 \
+        }                                                                                     \
+    } while (0)
+
+__global__ void owner_count_kernel(const uint64_t *__restrict__ codes, uint64_t n, uint32_t world,
+                                   unsigned long long *__restrict__ counts) {
+    __shared__ unsigned int sh[64];
+    if (threadIdx.x < 64) sh[threadIdx.x] = 0;
+    __syncthreads();
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) atomicAdd(&sh[mix64(codes[i]) % world], 1u);
+    __syncthreads();
+    if (threadIdx.x < world && sh[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
+}
+
+__global__ void owner_scatter_kernel(const uint64_t *__restrict__ codes, uint64_t n, uint32_t world,
+                                     unsigned long long *__restrict__ cursors, uint64_t *__restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t c = codes[i];
+    // order inside a bucket is irrelevant: the owner sorts what it receives
+    const unsigned long long slot = atomicAdd(&cursors[mix64(c) % world], 1ULL);
+    out[slot] = c;
+}
+
+__global__ void head_flags_keys_kernel(const uint64_t *__restrict__ keys, uint64_t n, uint32_t *__restrict__ flags) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u;
+}
+__global__ void compact_keys_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ flags,
+                                    const uint64_t *__restrict__ pos, uint64_t n, uint64_t *__restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && flags[i]) out[pos[i]] = keys[i];
+}
+
+static inline unsigned gridf(uint64_t n) { return (unsigned)((n + 255) / 256); }
+
+// In: g->node_codes holds this rank's sorted unique codes (g->n_nodes of them).
+// Out: g->node_codes holds the global sorted unique table, g->n_nodes its size.
+int comm_global_nodes(pdg_graph *g, int key_bits) {
+    NcclApi *api = nccl_api();
+    if (!api) return PDG_E_COMM;
+    if (g->world > 64) {
+        set_error("world size %d > 64", g->world);
+        return PDG_E_INVALID;
+    }
+    cudaStream_t s = g->stream;
+    ncclComm_t comm = reinterpret_cast<ncclComm_t>(g->nccl_comm);
+    const int W = g->world, R = g->rank;
+    const uint64_t n_loc = g->n_nodes;
+
+    // 1. bucket the local unique codes by owner
+    DevBuf d_counts, d_all_counts, d_send, d_recv;
+    d_counts.reserve(2 * W * 8, s);
+    d_all_counts.reserve((size_t)W * W * 8, s);
+    PDG_CUDA(cudaMemsetAsync(d_counts.p, 0, 2 * W * 8, s));
+    unsigned long long *counts = d_counts.as<unsigned long long>();
+    unsigned long long *cursors = counts + W;
+    if (n_loc) {
+        owner_count_kernel<<<gridf(n_loc), 256, 0, s>>>(g->node_codes.as<uint64_t>(), n_loc, W, counts);
+        PDG_LAUNCH_CHECK();
+    }
+    std::vector<uint64_t> h_send(W), h_all((size_t)W * W);
+    PDG_CUDA(cudaMemcpyAsync(h_send.data(), counts, W * 8, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    std::vector<uint64_t> send_off(W + 1, 0);
+    for (int p = 0; p < W; ++p) send_off[p + 1] = send_off[p] + h_send[p];
+    PDG_CUDA(cudaMemcpyAsync(cursors, send_off.data(), W * 8, cudaMemcpyHostToDevice, s));
+    d_send.reserve(std::max<size_t>(n_loc * 8, 16), s);
+    if (n_loc) {
+        owner_scatter_kernel<<<gridf(n_loc), 256, 0, s>>>(g->node_codes.as<uint64_t>(), n_loc, W, cursors,
+                                                         d_send.as<uint64_t>());
+        PDG_LAUNCH_CHECK();
+    }
+    // 2. counts matrix, then ONE grouped all-to-all of the codes
+    PDG_NCCL(api, api->AllGather(counts, d_all_counts.p, W, ncclUint64, comm, s));
+    PDG_CUDA(cudaMemcpyAsync(h_all.data(), d_all_counts.p, (size_t)W * W * 8, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    std::vector<uint64_t> recv_off(W + 1, 0);
+    for (int p = 0; p < W; ++p) recv_off[p + 1] = recv_off[p] + h_all[(size_t)p * W + R];   // p sends me this
+    const uint64_t n_recv = recv_off[W];
+    d_recv.reserve(std::max<size_t>(n_recv * 8, 16), s);
+    PDG_NCCL(api, api->GroupStart());
+    for (int p = 0; p < W; ++p) {
+        if (h_send[p]) PDG_NCCL(api, api->Send(d_send.as<uint64_t>() + send_off[p], h_send[p], ncclUint64, p, comm, s));
+        const uint64_t rc = h_all[(size_t)p * W + R];
+        if (rc) PDG_NCCL(api, api->Recv(d_recv.as<uint64_t>() + recv_off[p], rc, ncclUint64, p, comm, s));
+    }
+    PDG_NCCL(api, api->GroupEnd());
+
+    // 3. owner: sort + run-length compaction of what was received
+    uint64_t n_own = 0;
+    DevBuf d_own, d_tmp;
+    d_own.reserve(std::max<size_t>(n_recv * 8, 16), s);
+    if (n_recv) {
+        d_tmp.reserve(n_recv * 8, s);
+        uint64_t pr = 0;
+        uint64_t *sorted = radix_sort_keys(g, d_recv.as<uint64_t>(), d_tmp.as<uint64_t>(), n_recv, key_bits, &pr);
+        g->scratch0.reserve(n_recv * 4, s);
+        g->scratch1.reserve((n_recv + 1) * 8, s);
+        head_flags_keys_kernel<<<gridf(n_recv), 256, 0, s>>>(sorted, n_recv, g->scratch0.as<uint32_t>());
+        PDG_LAUNCH_CHECK();
+        exclusive_scan_u32_u64(g->scratch0.as<uint32_t>(), g->scratch1.as<uint64_t>(), n_recv, g);
+        PDG_CUDA(cudaMemcpyAsync(&n_own, g->scratch1.as<uint64_t>() + n_recv, 8, cudaMemcpyDeviceToHost, s));
+        PDG_CUDA(cudaStreamSynchronize(s));
+        compact_keys_kernel<<<gridf(n_recv), 256, 0, s>>>(sorted, g->scratch0.as<uint32_t>(),
+                                                         g->scratch1.as<uint64_t>(), n_recv, d_own.as<uint64_t>());
+        PDG_LAUNCH_CHECK();
+    }
+    // 4. all-gather the owned sets (they are disjoint) and sort once more
+    PDG_CUDA(cudaMemcpyAsync(counts, &n_own, 8, cudaMemcpyHostToDevice, s));
+    PDG_NCCL(api, api->AllGather(counts, d_all_counts.p, 1, ncclUint64, comm, s));
+    std::vector<uint64_t> own_counts(W);
+    PDG_CUDA(cudaMemcpyAsync(own_counts.data(), d_all_counts.p, W * 8, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    std::vector<uint64_t> own_off(W + 1, 0);
+    for (int p = 0; p < W; ++p) own_off[p + 1] = own_off[p] + own_counts[p];
+    const uint64_t n_glob = own_off[W];
+    DevBuf d_all, d_all2;
+    d_all.reserve(std::max<size_t>(n_glob * 8, 16), s);
+    d_all2.reserve(std::max<size_t>(n_glob * 8, 16), s);
+    PDG_NCCL(api, api->GroupStart());
+    for (int p = 0; p < W; ++p)
+        if (own_counts[p])
+            PDG_NCCL(api, api->Broadcast(d_own.p, d_all.as<uint64_t>() + own_off[p], own_counts[p], ncclUint64, p, comm, s));
+    PDG_NCCL(api, api->GroupEnd());
+    uint64_t *glob = d_all.as<uint64_t>();
+    if (n_glob > 1) {
+        uint64_t pr = 0;
+        glob = radix_sort_keys(g, d_all.as<uint64_t>(), d_all2.as<uint64_t>(), n_glob, key_bits, &pr);
+    }
+    g->node_codes.reserve(std::max<size_t>(n_glob * 8, 16), s);
+    if (n_glob) PDG_CUDA(cudaMemcpyAsync(g->node_codes.p, glob, n_glob * 8, cudaMemcpyDeviceToDevice, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    g->n_nodes = n_glob;
+    return PDG_OK;
+}
+
+}  // namespace pdg
+
+using namespace pdg;
+
+extern "C" {
+
+int pdg_comm_unique_id(uint8_t *h_id128) {
+    NcclApi *api = nccl_api();
+    if (!api) return PDG_E_COMM;
+    ncclUniqueId id;
+    ncclResult_t r = api->GetUniqueId(&id);
+    if (r != ncclSuccess) {
+        set_error("ncclGetUniqueId failed: %s", api->GetErrorString ? api->GetErrorString(r) : "?");
+        return PDG_E_COMM;
+    }
+    memcpy(h_id128, id.internal, NCCL_UNIQUE_ID_BYTES);
+    return PDG_OK;
+}
+
+int pdg_comm_init(pdg_graph *g, const uint8_t *h_id128, int rank, int world) {
+    if (!g) {
+        set_error("null graph handle");
+        return PDG_E_INVALID;
+    }
+    NcclApi *api = nccl_api();
+    if (!api) return PDG_E_COMM;
+    if (cudaSetDevice(g->device) != cudaSuccess) {
+        set_error("cudaSetDevice(%d) failed", g->device);
+        return PDG_E_CUDA;
+    }
+    ncclUniqueId id;
+    memcpy(id.internal, h_id128, NCCL_UNIQUE_ID_BYTES);
+    ncclComm_t comm;
+    ncclResult_t r = api->CommInitRank(&comm, world, id, rank);
+    if (r != ncclSuccess) {
+        set_error("ncclCommInitRank failed: %s", api->GetErrorString ? api->GetErrorString(r) : "?");
+        return PDG_E_COMM;
+    }
+    g->nccl_comm = comm;
+    g->rank = rank;
+    g->world = world;
+    return PDG_OK;
+}
+
+}  // extern "C"
