@@ -24,6 +24,20 @@
  * (the enumeration order of kmers.py:17-24 possible_kmers), k <= 31.  Codes with bit 63 set are
  * opaque node keys interned by the host (node values that are not clean k-mers, for example the
  * three letter names of tests/test_connected.py).  edge_value is a signed 32-bit integer.
+ *
+ * Data model.  A graph holds two disjoint parts that together are the reference's node set and
+ * labelled edge set:
+ *   G  genome part: 2-bit packed residues + a contig table + the k-mer OCCURRENCE INDEX
+ *      (positions of every k-mer occurrence, grouped by k-mer code, ascending position inside a
+ *      group).  A labelled edge (src, tgt, edge_type, edge_value) of subgraph_ref.py:71-80 is a
+ *      pure function of an occurrence position p inside contig c: src = kmer(p), tgt = kmer(p+1),
+ *      edge_type = type[c], edge_value = p - begin[c]; so the same index serves as the by-source
+ *      (out-edges: occurrences that are not last in their contig) and the by-target (in-edges:
+ *      occurrences that are not first) adjacency of lemongraph.c:603-630.
+ *   X  explicit part: edges / nodes given one at a time through the per-edge API, kept as
+ *      deduplicated CSR + CSC over their own node table.
+ * A contig whose type id is shared with another contig or with an explicit edge is expanded into
+ * X at pdg_finalize so that set semantics (lemongraph.c:674-685) stay exact.
  */
 #ifndef PDGPU_H
 #define PDGPU_H
@@ -34,7 +48,7 @@
 extern "C" {
 #endif
 
-#define PDG_ABI_VERSION 1
+#define PDG_ABI_VERSION 2
 
 #define PDG_OK            0
 #define PDG_E_INVALID    -1   /* bad argument / bad state */
@@ -56,23 +70,30 @@ typedef struct pdg_ingest_info {
 } pdg_ingest_info;
 
 /* one path-query hit: a occurs as the source of edge (type_id, i), b as the target of edge
- * (type_id, j), i <= j, j - i <= max_len  (lemon_graph.py:275-334, graph.py:82-113) */
+ * (type_id, j), i <= j, j - i <= max_len  (lemon_graph.py:275-334, graph.py:82-113).
+ * aux: for a hit in the genome part, the index of the contig in pdg_add_contigs order among the
+ * contigs kept in G (the path is residues [begin+i, begin+j+1+k) of that contig); for a hit in
+ * the explicit part, PDG_HIT_EXPLICIT | node id (in the X node table) of the start edge's target. */
+#define PDG_HIT_EXPLICIT 0x80000000u
 typedef struct pdg_hit {
     uint32_t type_id;
     int32_t  i;
     int32_t  j;
-    uint32_t src_tgt_id;     /* node id of the target of the start edge */
+    uint32_t aux;
 } pdg_hit;
 
 /* counters of the last pdg_finalize, for roofline accounting (bench.py) */
 typedef struct pdg_build_stats {
     uint64_t n_residues, n_contigs, n_kmers, n_edge_records, n_nodes, n_edges;
-    uint64_t node_path;      /* 0 = presence bitmap, 1 = radix sort + run-length compaction */
-    uint64_t general_sort;   /* 0 = fast path (records arrive sorted by (type,value)), 1 = full key */
-    uint64_t sort_passes_csr, sort_passes_csc;
-    float ms_nodes, ms_records, ms_sort_csr, ms_sort_csc, ms_pack_csr, ms_pack_csc, ms_total;
-    float ms_onesweep_avg;   /* average duration of one onesweep pass kernel */
-    uint64_t onesweep_launches, onesweep_records;
+    uint64_t node_path;      /* 0 = presence bitmap lookup, 1 = binary search over sorted codes */
+    uint64_t n_demoted;      /* contigs expanded into the explicit part */
+    uint64_t sort_passes;    /* partition passes run for the occurrence index */
+    uint64_t sort_records;   /* records per pass */
+    float ms_upload, ms_nodes, ms_sort, ms_rows, ms_explicit, ms_total;
+    float ms_sort_kernel_avg;   /* CUDA-event average of one partition pass kernel */
+    float pad;
+    uint64_t sort_kernel_launches;
+    uint64_t kernel_launches;   /* kernels launched by the last pdg_finalize */
 } pdg_build_stats;
 
 const char *pdg_last_error(void);
@@ -105,8 +126,10 @@ int pdg_add_contigs(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len
 int pdg_kmer_stats(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len,
                    uint64_t n_contigs, uint64_t *n_kmers, uint64_t *n_unique);
 
-/* k-mer codes of one contig (device output, n = len-k+1 codes); Kmers.next as a bulk call. */
+/* k-mer codes of residues [begin, begin+len) (device output, n = len-k+1 codes); Kmers.next as
+ * a bulk call.  pdg_fetch_residues decodes the same range back to ASCII (host output). */
 int pdg_emit_codes(pdg_graph *g, uint64_t begin, uint64_t len, uint64_t *d_codes_out);
+int pdg_fetch_residues(pdg_graph *g, uint64_t begin, uint64_t len, uint8_t *h_ascii);
 
 /* Per-edge compatibility path: LGGraph.add_edge / upsert_node (lemon_graph.py:99-128) and
  * graph_edge_resolve / graph_node_resolve (cffi_stubs.py).  Host arrays are copied. */
@@ -114,9 +137,10 @@ int pdg_add_edges_host(pdg_graph *g, const uint64_t *h_src_code, const uint64_t 
                        const uint32_t *h_type_id, const int32_t *h_value, uint64_t n);
 int pdg_add_nodes_host(pdg_graph *g, const uint64_t *h_code, uint64_t n);
 
-/* K2+K3: node dedup -> dense ids, edge dedup -> CSR + CSC.  Replaces the LMDB upserts behind
- * LGGraph.add_edge + LGGraph.save (lemon_graph.py:115-128,154-157; lemongraph.c:661-685).
- * flags: bit0 = force the radix-sort node path, bit1 = force the full-key edge sort. */
+/* K2+K3: node dedup -> dense ids, occurrence index (G) and CSR + CSC (X).  Replaces the LMDB
+ * upserts behind LGGraph.add_edge + LGGraph.save (lemon_graph.py:115-128,154-157;
+ * lemongraph.c:661-685).  flags: bit0 = never use the bitmap lookup, bit1 = expand every contig
+ * into the explicit part (general path, used by the parity tests). */
 #define PDG_F_FORCE_SORT_NODES 1
 #define PDG_F_FORCE_GENERAL    2
 int pdg_finalize(pdg_graph *g, int flags);
@@ -124,31 +148,39 @@ int pdg_counts(pdg_graph *g, uint64_t *n_nodes, uint64_t *n_edges, uint64_t *n_k
 int pdg_get_build_stats(pdg_graph *g, pdg_build_stats *out);
 
 /* LGGraph.nodes / edges (lemon_graph.py:133-149).  Outputs are HOST arrays sized from
- * pdg_counts.  Nodes come in ascending code order (id = index); edges in CSR order, i.e. sorted by
- * (src id, type id, value, tgt id).  Any output pointer may be NULL. */
+ * pdg_counts.  Nodes come in ascending code order (dense node id = index).  Edges: first the
+ * genome part in index order (ascending (src code, position)), then the explicit part in CSR
+ * order.  Any output pointer may be NULL. */
 int pdg_export_nodes(pdg_graph *g, uint64_t *h_codes);
-int pdg_export_edges(pdg_graph *g, uint32_t *h_src_id, uint32_t *h_tgt_id, uint32_t *h_type_id,
-                     int32_t *h_value);
+int pdg_export_edges(pdg_graph *g, uint64_t *h_src_code, uint64_t *h_tgt_code,
+                     uint32_t *h_type_id, int32_t *h_value);
+/* dense node ids (rank in pdg_export_nodes order) of the given codes; UINT64_MAX if absent */
+int pdg_node_ids(pdg_graph *g, const uint64_t *h_codes, uint64_t n, uint64_t *h_ids);
+/* raw occurrence index of the genome part: h_row_codes[n_rows], h_row_ptr[n_rows+1],
+ * h_positions[n_kmers] (sizes from pdg_index_size) */
+int pdg_index_size(pdg_graph *g, uint64_t *n_rows, uint64_t *n_positions);
+int pdg_export_index(pdg_graph *g, uint64_t *h_row_codes, uint32_t *h_row_ptr, uint32_t *h_positions);
 /* order-independent 64-bit checksums of the canonical node set and edge set (sum of a mixed
- * hash over (code) / (src code, tgt code, type, value)), computed on the device */
+ * hash over (code) / (src code, tgt code, type, value)), computed on the device from the index */
 int pdg_checksum(pdg_graph *g, uint64_t *nodes_sum, uint64_t *edges_sum);
 
 /* K4: batched queries.  h_a/h_b are node codes.  pdg_query_connected replaces LGGraph.connected
- * (lemon_graph.py:178-219): per query the number of start edges.  pdg_query_paths replaces
- * LGGraph.path (lemon_graph.py:275-334): hits per query with j - i <= max_len.  Results stay in
- * graph-owned device memory until the next query call; pdg_query_fetch copies them to the host
- * (h_offsets has n_q + 1 entries).  pdg_query_walk materialises the node ids of one hit's path
- * (_find_path, lemon_graph.py:221-273): n = j - i + 2 ids; status 0 ok, 1 broken, 2 ambiguous. */
+ * (lemon_graph.py:178-219): per query the start edges.  pdg_query_paths replaces
+ * LGGraph.path (lemon_graph.py:275-334): hits per query with j - i <= max_len (max_len < 0: no
+ * limit).  Results stay in graph-owned device memory until the next query call; pdg_query_fetch
+ * copies them to the host (h_offsets has n_q + 1 entries).  pdg_query_walk materialises the node
+ * codes of one hit's path (_find_path, lemon_graph.py:221-273): n = j - i + 2 codes; status 0 ok,
+ * 1 chain broken, 2 ambiguous (the reference's `assert len(chains) == 1` would fail). */
 int pdg_query_connected(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q,
                         uint64_t *total_starts);
 int pdg_query_paths(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q,
                     int64_t max_len, uint64_t *total_hits);
 int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits);
-int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint32_t *h_node_ids,
+int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_node_codes,
                    int32_t *status);
 
 /* K5: multi-GPU (one process per GPU).  The host exchanges the 128-byte id with
- * torch.distributed; records are hash partitioned with one grouped ncclSend/ncclRecv exchange
+ * torch.distributed; node keys are hash partitioned with one grouped ncclSend/ncclRecv exchange
  * inside pdg_finalize.  No reference counterpart. */
 int pdg_comm_unique_id(uint8_t *h_id128);
 int pdg_comm_init(pdg_graph *g, const uint8_t *h_id128, int rank, int world);

@@ -64,6 +64,8 @@ void pdg_destroy(pdg_graph *g) {
     if (!g) return;
     cudaSetDevice(g->device);
     cudaStreamSynchronize(g->stream);
+    if (g->ev0) cudaEventDestroy(g->ev0);
+    if (g->ev1) cudaEventDestroy(g->ev1);
     delete g;
 }
 
@@ -79,12 +81,14 @@ int pdg_clear(pdg_graph *g) {
     PDG_CUDA(cudaStreamSynchronize(g->stream));
     g->n_res = 0;
     if (g->packed.p) PDG_CUDA(cudaMemsetAsync(g->packed.p, 0, g->packed.cap, g->stream));
-    g->c_begin.clear(); g->c_len.clear(); g->c_edge_base.clear(); g->c_type.clear();
-    g->n_kmers = g->n_gen_edges = 0;
-    g->contigs_sorted_fresh = true;
+    g->c_begin.clear(); g->c_len.clear(); g->c_type.clear();
+    g->g_begin.clear(); g->g_len.clear(); g->g_type.clear();
+    g->n_kmers = 0;
     g->x_src.clear(); g->x_tgt.clear(); g->x_nodes.clear(); g->x_type.clear(); g->x_val.clear();
     g->finalized = false;
     g->n_nodes = g->n_edges = 0;
+    g->g_kmers = g->g_edges = g->g_nodes = 0;
+    g->x_n_nodes = g->x_n_edges = 0;
     g->q_n = g->q_total = 0;
     return PDG_OK;
     PDG_API_END
@@ -117,17 +121,9 @@ int pdg_add_contigs(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len
             set_error("pdg_add_contigs: contigs must be ascending and disjoint");
             return PDG_E_INVALID;
         }
-        if (!g->c_type.empty()) {
-            uint32_t mx = 0;
-            // strictly increasing type ids keep the generated records sorted by (type, value)
-            mx = g->c_type.back();
-            if (h_type_id[i] <= mx) g->contigs_sorted_fresh = false;
-        }
         g->c_begin.push_back(h_begin[i]);
         g->c_len.push_back(h_len[i]);
         g->c_type.push_back(h_type_id[i]);
-        g->c_edge_base.push_back(g->n_gen_edges);
-        g->n_gen_edges += h_len[i] - k;
         g->n_kmers += h_len[i] - k + 1;
     }
     g->finalized = false;
@@ -145,6 +141,12 @@ int pdg_kmer_stats(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len,
 int pdg_emit_codes(pdg_graph *g, uint64_t begin, uint64_t len, uint64_t *d_codes_out) {
     PDG_API_BEGIN
     return emit_codes(g, begin, len, d_codes_out);
+    PDG_API_END
+}
+
+int pdg_fetch_residues(pdg_graph *g, uint64_t begin, uint64_t len, uint8_t *h_ascii) {
+    PDG_API_BEGIN
+    return fetch_residues(g, begin, len, h_ascii);
     PDG_API_END
 }
 
@@ -202,32 +204,47 @@ int pdg_export_nodes(pdg_graph *g, uint64_t *h_codes) {
     PDG_API_BEGIN
     if (need_final(g, "pdg_export_nodes")) return PDG_E_INVALID;
     if (h_codes && g->n_nodes)
-        PDG_CUDA(cudaMemcpyAsync(h_codes, g->node_codes.p, g->n_nodes * 8, cudaMemcpyDeviceToHost, g->stream));
+        PDG_CUDA(cudaMemcpyAsync(h_codes, g->u_codes, g->n_nodes * 8, cudaMemcpyDeviceToHost, g->stream));
     PDG_CUDA(cudaStreamSynchronize(g->stream));
     return PDG_OK;
     PDG_API_END
 }
 
-int pdg_export_edges(pdg_graph *g, uint32_t *h_src_id, uint32_t *h_tgt_id, uint32_t *h_type_id, int32_t *h_value) {
+int pdg_export_edges(pdg_graph *g, uint64_t *h_src_code, uint64_t *h_tgt_code, uint32_t *h_type_id,
+                     int32_t *h_value) {
     PDG_API_BEGIN
     if (need_final(g, "pdg_export_edges")) return PDG_E_INVALID;
+    return export_edges(g, h_src_code, h_tgt_code, h_type_id, h_value);
+    PDG_API_END
+}
+
+int pdg_node_ids(pdg_graph *g, const uint64_t *h_codes, uint64_t n, uint64_t *h_ids) {
+    PDG_API_BEGIN
+    if (need_final(g, "pdg_node_ids")) return PDG_E_INVALID;
+    return node_ids(g, h_codes, n, h_ids);
+    PDG_API_END
+}
+
+int pdg_index_size(pdg_graph *g, uint64_t *n_rows, uint64_t *n_positions) {
+    PDG_API_BEGIN
+    if (need_final(g, "pdg_index_size")) return PDG_E_INVALID;
+    if (n_rows) *n_rows = g->g_nodes;
+    if (n_positions) *n_positions = g->g_kmers;
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_export_index(pdg_graph *g, uint64_t *h_row_codes, uint32_t *h_row_ptr, uint32_t *h_positions) {
+    PDG_API_BEGIN
+    if (need_final(g, "pdg_export_index")) return PDG_E_INVALID;
     cudaStream_t s = g->stream;
-    const uint64_t ne = g->n_edges, nn = g->n_nodes;
-    if (ne == 0) return PDG_OK;
-    if (h_tgt_id) PDG_CUDA(cudaMemcpyAsync(h_tgt_id, g->csr_tgt.p, ne * 4, cudaMemcpyDeviceToHost, s));
-    if (h_type_id) PDG_CUDA(cudaMemcpyAsync(h_type_id, g->csr_type.p, ne * 4, cudaMemcpyDeviceToHost, s));
-    if (h_value) PDG_CUDA(cudaMemcpyAsync(h_value, g->csr_val.p, ne * 4, cudaMemcpyDeviceToHost, s));
-    std::vector<uint64_t> rp;
-    if (h_src_id) {
-        rp.resize(nn + 1);
-        PDG_CUDA(cudaMemcpyAsync(rp.data(), g->row_ptr.p, (nn + 1) * 8, cudaMemcpyDeviceToHost, s));
-    }
+    if (h_row_codes && g->g_nodes)
+        PDG_CUDA(cudaMemcpyAsync(h_row_codes, g->g_codes.p, g->g_nodes * 8, cudaMemcpyDeviceToHost, s));
+    if (h_row_ptr)
+        PDG_CUDA(cudaMemcpyAsync(h_row_ptr, g->g_rowptr.p, (g->g_nodes + 1) * 4, cudaMemcpyDeviceToHost, s));
+    if (h_positions && g->g_kmers)
+        PDG_CUDA(cudaMemcpyAsync(h_positions, g->g_pos.p, g->g_kmers * 4, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
-    if (h_value)
-        for (uint64_t e = 0; e < ne; ++e) h_value[e] = (int32_t)((uint32_t)h_value[e] ^ 0x80000000u);
-    if (h_src_id)
-        for (uint64_t v = 0; v < nn; ++v)
-            for (uint64_t e = rp[v]; e < rp[v + 1]; ++e) h_src_id[e] = (uint32_t)v;
     return PDG_OK;
     PDG_API_END
 }
@@ -264,9 +281,9 @@ int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits) {
     PDG_API_END
 }
 
-int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint32_t *h_node_ids, int32_t *status) {
+int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_node_codes, int32_t *status) {
     PDG_API_BEGIN
-    return query_walk(g, src_code, hit, h_node_ids, status);
+    return query_walk(g, src_code, hit, h_node_codes, status);
     PDG_API_END
 }
 

@@ -107,9 +107,9 @@ __global__ void compact_keys_kernel(const uint64_t *__restrict__ keys, const uin
 
 static inline unsigned gridf(uint64_t n) { return (unsigned)((n + 255) / 256); }
 
-// In: g->node_codes holds this rank's sorted unique codes (g->n_nodes of them).
-// Out: g->node_codes holds the global sorted unique table, g->n_nodes its size.
-int comm_global_nodes(pdg_graph *g, int key_bits) {
+// In: d_local holds this rank's sorted unique codes (n_loc of them; may alias g->u_codes_buf).
+// Out: g->u_codes_buf holds the global sorted unique table, *n_global its size.
+int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int key_bits, uint64_t *n_global) {
     NcclApi *api = nccl_api();
     if (!api) return PDG_E_COMM;
     if (g->world > 64) {
@@ -119,7 +119,6 @@ int comm_global_nodes(pdg_graph *g, int key_bits) {
     cudaStream_t s = g->stream;
     ncclComm_t comm = reinterpret_cast<ncclComm_t>(g->nccl_comm);
     const int W = g->world, R = g->rank;
-    const uint64_t n_loc = g->n_nodes;
 
     // 1. bucket the local unique codes by owner
     DevBuf d_counts, d_all_counts, d_send, d_recv;
@@ -129,8 +128,8 @@ int comm_global_nodes(pdg_graph *g, int key_bits) {
     unsigned long long *counts = d_counts.as<unsigned long long>();
     unsigned long long *cursors = counts + W;
     if (n_loc) {
-        owner_count_kernel<<<gridf(n_loc), 256, 0, s>>>(g->node_codes.as<uint64_t>(), n_loc, W, counts);
-        PDG_LAUNCH_CHECK();
+        owner_count_kernel<<<gridf(n_loc), 256, 0, s>>>(d_local, n_loc, W, counts);
+        PDG_LAUNCHED(g);
     }
     std::vector<uint64_t> h_send(W), h_all((size_t)W * W);
     PDG_CUDA(cudaMemcpyAsync(h_send.data(), counts, W * 8, cudaMemcpyDeviceToHost, s));
@@ -140,9 +139,9 @@ int comm_global_nodes(pdg_graph *g, int key_bits) {
     PDG_CUDA(cudaMemcpyAsync(cursors, send_off.data(), W * 8, cudaMemcpyHostToDevice, s));
     d_send.reserve(std::max<size_t>(n_loc * 8, 16), s);
     if (n_loc) {
-        owner_scatter_kernel<<<gridf(n_loc), 256, 0, s>>>(g->node_codes.as<uint64_t>(), n_loc, W, cursors,
+        owner_scatter_kernel<<<gridf(n_loc), 256, 0, s>>>(d_local, n_loc, W, cursors,
                                                          d_send.as<uint64_t>());
-        PDG_LAUNCH_CHECK();
+        PDG_LAUNCHED(g);
     }
     // 2. counts matrix, then ONE grouped all-to-all of the codes
     PDG_NCCL(api, api->AllGather(counts, d_all_counts.p, W, ncclUint64, comm, s));
@@ -167,17 +166,17 @@ int comm_global_nodes(pdg_graph *g, int key_bits) {
     if (n_recv) {
         d_tmp.reserve(n_recv * 8, s);
         uint64_t pr = 0;
-        uint64_t *sorted = radix_sort_keys(g, d_recv.as<uint64_t>(), d_tmp.as<uint64_t>(), n_recv, key_bits, &pr);
+        uint64_t *sorted = radix_sort_keys(g, d_recv.as<uint64_t>(), d_tmp.as<uint64_t>(), n_recv, 0, key_bits, &pr);
         g->scratch0.reserve(n_recv * 4, s);
         g->scratch1.reserve((n_recv + 1) * 8, s);
         head_flags_keys_kernel<<<gridf(n_recv), 256, 0, s>>>(sorted, n_recv, g->scratch0.as<uint32_t>());
-        PDG_LAUNCH_CHECK();
+        PDG_LAUNCHED(g);
         exclusive_scan_u32_u64(g->scratch0.as<uint32_t>(), g->scratch1.as<uint64_t>(), n_recv, g);
         PDG_CUDA(cudaMemcpyAsync(&n_own, g->scratch1.as<uint64_t>() + n_recv, 8, cudaMemcpyDeviceToHost, s));
         PDG_CUDA(cudaStreamSynchronize(s));
         compact_keys_kernel<<<gridf(n_recv), 256, 0, s>>>(sorted, g->scratch0.as<uint32_t>(),
                                                          g->scratch1.as<uint64_t>(), n_recv, d_own.as<uint64_t>());
-        PDG_LAUNCH_CHECK();
+        PDG_LAUNCHED(g);
     }
     // 4. all-gather the owned sets (they are disjoint) and sort once more
     PDG_CUDA(cudaMemcpyAsync(counts, &n_own, 8, cudaMemcpyHostToDevice, s));
@@ -199,12 +198,13 @@ int comm_global_nodes(pdg_graph *g, int key_bits) {
     uint64_t *glob = d_all.as<uint64_t>();
     if (n_glob > 1) {
         uint64_t pr = 0;
-        glob = radix_sort_keys(g, d_all.as<uint64_t>(), d_all2.as<uint64_t>(), n_glob, key_bits, &pr);
+        glob = radix_sort_keys(g, d_all.as<uint64_t>(), d_all2.as<uint64_t>(), n_glob, 0, key_bits, &pr);
     }
-    g->node_codes.reserve(std::max<size_t>(n_glob * 8, 16), s);
-    if (n_glob) PDG_CUDA(cudaMemcpyAsync(g->node_codes.p, glob, n_glob * 8, cudaMemcpyDeviceToDevice, s));
+    PDG_CUDA(cudaStreamSynchronize(s));   // d_local (which may live in u_codes_buf) is no longer read
+    g->u_codes_buf.reserve(std::max<size_t>(n_glob * 8, 16), s);
+    if (n_glob) PDG_CUDA(cudaMemcpyAsync(g->u_codes_buf.p, glob, n_glob * 8, cudaMemcpyDeviceToDevice, s));
     PDG_CUDA(cudaStreamSynchronize(s));
-    g->n_nodes = n_glob;
+    *n_global = n_glob;
     return PDG_OK;
 }
 

@@ -111,38 +111,53 @@ struct pdg_graph {
     int device = 0;
     int k = 11;
     cudaStream_t stream = nullptr;
+    uint64_t launches = 0;         // kernels launched (reset by pdg_finalize)
 
     // ---- genome store: residues packed 2 bits each, big endian inside 64-bit words ----
     pdg::DevBuf packed;            // uint64 words, zero beyond n_res
     uint64_t n_res = 0;
-    std::vector<uint64_t> c_begin, c_len, c_edge_base;   // valid contigs (len > k), ascending begin
+    // every declared contig with len > k, ascending begin
+    std::vector<uint64_t> c_begin, c_len;
     std::vector<uint32_t> c_type;
-    uint64_t n_kmers = 0;          // sum(len-k+1) over valid contigs
-    uint64_t n_gen_edges = 0;      // sum(len-k)
-    bool contigs_sorted_fresh = true;   // type ids strictly increasing with begin => fast path
+    uint64_t n_kmers = 0;          // sum(len-k+1) over declared contigs
 
     // ---- explicit (per-edge API) staging, host side until finalize ----
     std::vector<uint64_t> x_src, x_tgt, x_nodes;
     std::vector<uint32_t> x_type;
     std::vector<int32_t> x_val;
 
-    // ---- finalized graph ----
     bool finalized = false;
-    uint64_t n_nodes = 0, n_edges = 0;
-    pdg::DevBuf node_codes;        // uint64[n_nodes], ascending
-    pdg::DevBuf row_ptr, col_ptr;  // uint64[n_nodes+1]
-    pdg::DevBuf csr_tgt, csr_type, csr_val;   // uint32[n_edges]; val biased (^0x80000000)
-    pdg::DevBuf csc_src, csc_type, csc_val;
-    // node lookup: presence bitmap + exclusive popcount prefix (bitmap path)
-    bool have_bitmap = false;
+    uint64_t n_nodes = 0, n_edges = 0;   // whole graph (n_nodes: global when world > 1)
+
+    // ---- G: genome part = occurrence index over the contigs that stayed in G ----
+    std::vector<uint64_t> g_begin, g_len;    // host copy (ascending begin)
+    std::vector<uint32_t> g_type;
+    uint64_t g_kmers = 0, g_edges = 0, g_nodes = 0;
+    pdg::DevBuf d_gbegin, d_gend, d_gkbase, d_gtype;   // device contig table (kbase: k-mers before)
+    pdg::DevBuf g_codes;           // uint64[g_nodes] ascending = the rows
+    pdg::DevBuf g_rowptr;          // uint32[g_nodes+1]
+    pdg::DevBuf g_pos;             // uint32[g_kmers] residue positions, by (code, position)
+    bool have_bitmap = false;      // presence bitmap + exclusive popcount prefix over g_codes
     uint64_t bitmap_words = 0;     // 32-bit words
     pdg::DevBuf bitmap, bitmap_prefix;
 
+    // ---- X: explicit part (per-edge API content and demoted contigs) ----
+    uint64_t x_n_nodes = 0, x_n_edges = 0;
+    pdg::DevBuf x_codes;           // uint64[x_n_nodes] ascending
+    pdg::DevBuf row_ptr, col_ptr;  // uint64[x_n_nodes+1]
+    pdg::DevBuf csr_tgt, csr_type, csr_val;   // uint32[x_n_edges]; val biased (^0x80000000)
+    pdg::DevBuf csc_src, csc_type, csc_val;
+
+    // ---- node table of the whole graph (G union X; all ranks when world > 1) ----
+    pdg::DevBuf u_codes_buf;
+    const uint64_t *u_codes = nullptr;   // points at g_codes, x_codes or u_codes_buf
+
     // ---- scratch ----
-    pdg::DevBuf d_cbegin, d_cend, d_cebase, d_ctype;     // device copy of the contig table
     pdg::DevBuf recA, recB, scratch0, scratch1, scratch2, status, hist;
-    pdg::DevBuf q_a, q_b, q_cnt, q_off, q_hits, small;
+    pdg::DevBuf q_a, q_b, q_cnt, q_cnt_g, q_off, q_hits, small;
     uint64_t q_n = 0, q_total = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool collect_sort_stats = false;   // radix.cu times its pass kernels into stats
 
     pdg_build_stats stats{};
 
@@ -150,6 +165,8 @@ struct pdg_graph {
     void *nccl_comm = nullptr;
     int rank = 0, world = 1;
 };
+
+#define PDG_LAUNCHED(g) do { ++(g)->launches; PDG_LAUNCH_CHECK(); } while (0)
 
 namespace pdg {
 
@@ -164,7 +181,8 @@ void exclusive_scan_u32_u32(const uint32_t *d_in, uint32_t *d_out, uint64_t n, p
 // buffer (a or b) that holds the result.  Stable.
 EdgeRec *radix_sort_records(pdg_graph *g, EdgeRec *a, EdgeRec *b, uint64_t n,
                             const std::vector<PassDesc> &passes, uint64_t *passes_run);
-uint64_t *radix_sort_keys(pdg_graph *g, uint64_t *a, uint64_t *b, uint64_t n, int key_bits,
+// sorts on key bits [lo_bit, hi_bit)
+uint64_t *radix_sort_keys(pdg_graph *g, uint64_t *a, uint64_t *b, uint64_t n, int lo_bit, int hi_bit,
                           uint64_t *passes_run);
 
 // ---- ingest.cu ----
@@ -172,20 +190,25 @@ int ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes, uint64_
                  uint64_t cap_headers, pdg_ingest_info *info);
 
 // ---- build.cu ----
-void upload_contigs(pdg_graph *g);
 int finalize(pdg_graph *g, int flags);
 int kmer_stats(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len, uint64_t n,
                uint64_t *n_kmers, uint64_t *n_unique);
 int emit_codes(pdg_graph *g, uint64_t begin, uint64_t len, uint64_t *d_out);
+int fetch_residues(pdg_graph *g, uint64_t begin, uint64_t len, uint8_t *h_ascii);
 int checksum(pdg_graph *g, uint64_t *nodes_sum, uint64_t *edges_sum);
+int export_edges(pdg_graph *g, uint64_t *h_src, uint64_t *h_tgt, uint32_t *h_type, int32_t *h_val);
+int node_ids(pdg_graph *g, const uint64_t *h_codes, uint64_t n, uint64_t *h_ids);
+// sorted unique codes of `keys` (n of them, destroyed) -> out (reserved here); returns the count
+uint64_t sort_unique_keys(pdg_graph *g, uint64_t *keys, uint64_t *tmp, uint64_t n, int key_bits, DevBuf &out);
 
 // ---- query.cu ----
 int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q, int64_t max_len,
               bool connected_only, uint64_t *total);
-int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint32_t *h_ids, int32_t *status);
+int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_codes, int32_t *status);
 
 // ---- comm.cu ----
-// replaces g->node_codes (this rank's sorted unique codes) by the global table (all ranks)
-int comm_global_nodes(pdg_graph *g, int key_bits);
+// in: sorted unique codes of this rank (d_local, n_local); out: g->u_codes_buf holds the global
+// sorted unique table of all ranks, *n_global its size
+int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_local, int key_bits, uint64_t *n_global);
 
 }  // namespace pdg

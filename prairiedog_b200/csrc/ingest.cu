@@ -345,9 +345,9 @@ int ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes, uint64_
     TilePrefix *d_prefix = g->scratch1.as<TilePrefix>();
     IngestTotals *d_tot = reinterpret_cast<IngestTotals *>(g->scratch1.as<unsigned char>() + n_tiles * sizeof(TilePrefix));
     fasta_tile_summaries<<<(unsigned)n_tiles, IN_THREADS, 0, s>>>(d_bytes, n_bytes, d_summ);
-    PDG_LAUNCH_CHECK();
+    PDG_LAUNCHED(g);
     fasta_tile_scan<<<1, IN_THREADS, 0, s>>>(d_summ, n_tiles, d_prefix, d_tot);
-    PDG_LAUNCH_CHECK();
+    PDG_LAUNCHED(g);
     IngestTotals tot{};
     PDG_CUDA(cudaMemcpyAsync(&tot, d_tot, sizeof(tot), cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
@@ -378,7 +378,7 @@ int ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes, uint64_
     }
     fasta_emit<<<(unsigned)n_tiles, IN_THREADS, 0, s>>>(d_bytes, n_bytes, d_prefix, d_packed,
                                                         append ? g->n_res : 0, d_table, tot.hdr);
-    PDG_LAUNCH_CHECK();
+    PDG_LAUNCHED(g);
     if (tot.hdr) {
         PDG_CUDA(cudaMemcpyAsync(h_header_table, d_table, tot.hdr * 3 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
     }

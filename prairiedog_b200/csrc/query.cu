@@ -1,15 +1,19 @@
-// query.cu -- K4: batched "all paths between two k-mers" over the CSR/CSC.
+// query.cu -- K4: batched "all paths between two k-mers".
 //
 // Restates LGGraph.connected / path (prairiedog/lemon_graph.py:178-334) and Graph.matching_edges
-// (prairiedog/graph.py:82-113).  Out-edges of a (CSR row) and in-edges of b (CSC row) are both
-// sorted by (type id, value); a start edge (T,i) matches every in-edge (T,j) with i <= j
-// (and j - i <= max_len for path()), which is one contiguous range found by binary search.
+// (prairiedog/graph.py:82-113): a start edge (T,i) out of a matches every edge (T,j) into b with
+// i <= j (and j - i <= max_len for path()).
+//   genome part: a's row and b's row of the occurrence index are ascending position lists.  An
+//     occurrence p of a inside contig c is a start edge (T=type[c], i=p-begin[c]) unless it is the
+//     last k-mer of c; the matching in-edges of b are its occurrences q in [p+1, min(p+1+max_len,
+//     end[c]-k)], one contiguous range of b's row found by binary search (j = q-begin[c]-1).
+//   explicit part: CSR row of a and CSC row of b are sorted by (type, value); same range search.
 // One warp per query; a count launch, a prefix sum, then a fill launch.
-#include "common.cuh"
+#include "gindex.cuh"
 
 namespace pdg {
 
-struct GraphView {
+struct XView {
     const uint64_t *codes;
     uint64_t n_nodes;
     const uint64_t *row_ptr;
@@ -18,10 +22,17 @@ struct GraphView {
     const uint32_t *csc_src, *csc_type, *csc_val;
 };
 
-static GraphView view_of(const pdg_graph *g) {
-    GraphView v;
-    v.codes = g->node_codes.as<uint64_t>();
-    v.n_nodes = g->n_nodes;
+struct GView {
+    NodeLookup L;
+    const uint32_t *rowptr, *pos;
+    ContigTable ct;
+    int k;
+};
+
+static XView xview_of(const pdg_graph *g) {
+    XView v;
+    v.codes = g->x_codes.as<uint64_t>();
+    v.n_nodes = g->x_n_nodes;
     v.row_ptr = g->row_ptr.as<uint64_t>();
     v.csr_tgt = g->csr_tgt.as<uint32_t>();
     v.csr_type = g->csr_type.as<uint32_t>();
@@ -33,19 +44,93 @@ static GraphView view_of(const pdg_graph *g) {
     return v;
 }
 
-__device__ __forceinline__ int64_t find_node(const GraphView &G, uint64_t code) {
-    uint64_t lo = 0, hi = G.n_nodes;
-    while (lo < hi) {
-        const uint64_t mid = (lo + hi) >> 1;
-        if (G.codes[mid] < code) lo = mid + 1; else hi = mid;
-    }
-    return (lo < G.n_nodes && G.codes[lo] == code) ? (int64_t)lo : -1;
+static GView gview_of(const pdg_graph *g) {
+    GView v;
+    v.L = g_lookup(g);
+    v.rowptr = g->g_rowptr.as<uint32_t>();
+    v.pos = g->g_pos.as<uint32_t>();
+    v.ct = g_table(g);
+    v.k = g->k;
+    return v;
 }
 
+__device__ __forceinline__ uint64_t warp_excl_scan(uint64_t cnt, int lane, uint64_t *wtot) {
+    uint64_t inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint64_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    *wtot = __shfl_sync(0xffffffffu, inc, 31);
+    return inc - cnt;
+}
+
+// first index in [lo,hi) with pos[index] >= key
+__device__ __forceinline__ uint64_t lower_bound_pos(const uint32_t *pos, uint64_t lo, uint64_t hi, uint64_t key) {
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        if ((uint64_t)pos[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// ---- genome part ----
+template <bool FILL>
+__global__ void __launch_bounds__(256) gquery_kernel(GView G, const uint64_t *__restrict__ qa,
+                                                     const uint64_t *__restrict__ qb, uint64_t n_q, int64_t max_len,
+                                                     int connected, uint32_t *__restrict__ counts,
+                                                     const uint64_t *__restrict__ offsets, pdg_hit *__restrict__ hits) {
+    const uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (q >= n_q) return;
+    const int64_t ia = find_code(G.L, qa[q]);
+    const int64_t ib = find_code(G.L, qb[q]);
+    uint64_t total = 0;
+    if (ia >= 0 && ib >= 0) {
+        const uint64_t o0 = G.rowptr[ia], o1 = G.rowptr[ia + 1];
+        const uint64_t i0 = G.rowptr[ib], i1 = G.rowptr[ib + 1];
+        uint64_t out_base = FILL ? offsets[q] : 0;
+        for (uint64_t base = o0; base < o1; base += 32) {
+            const uint64_t e = base + lane;
+            uint64_t lo = 0, cnt = 0, c = 0, p = 0, cb = 0;
+            if (e < o1) {
+                p = G.pos[e];
+                c = contig_of(G.ct, p);
+                cb = G.ct.begin[c];
+                const uint64_t ce = G.ct.end[c];
+                if (p + G.k < ce) {                       // not the last k-mer: an out-edge (T, p-cb)
+                    uint64_t qmax = ce - G.k;            // last k-mer start of the contig
+                    if (!connected && max_len >= 0) qmax = min(qmax, p + 1 + (uint64_t)max_len);
+                    lo = lower_bound_pos(G.pos, i0, i1, p + 1);
+                    const uint64_t hi = lower_bound_pos(G.pos, lo, i1, qmax + 1);
+                    cnt = hi - lo;
+                    if (connected) cnt = cnt ? 1 : 0;
+                }
+            }
+            uint64_t wtot;
+            const uint64_t excl = warp_excl_scan(cnt, lane, &wtot);
+            if (FILL && cnt) {
+                pdg_hit *dst = hits + out_base + excl;
+                for (uint64_t t = 0; t < cnt; ++t) {
+                    pdg_hit h;
+                    h.type_id = G.ct.type[c];
+                    h.i = (int32_t)(p - cb);
+                    h.j = connected ? h.i : (int32_t)((uint64_t)G.pos[lo + t] - cb - 1);
+                    h.aux = (uint32_t)c;
+                    dst[t] = h;
+                }
+            }
+            out_base += wtot;
+            total += wtot;
+        }
+    }
+    if (!FILL && lane == 0) counts[q] = (uint32_t)min(total, (uint64_t)0xFFFFFFFFu);
+}
+
+// ---- explicit part ----
 __device__ __forceinline__ uint64_t tv_key(const uint32_t *type, const uint32_t *val, uint64_t e) {
     return ((uint64_t)type[e] << 32) | (uint64_t)val[e];
 }
-// first index in [lo,hi) whose (type,val) key is >= key
 __device__ __forceinline__ uint64_t lower_bound_tv(const uint32_t *type, const uint32_t *val, uint64_t lo, uint64_t hi,
                                                    uint64_t key) {
     while (lo < hi) {
@@ -54,7 +139,6 @@ __device__ __forceinline__ uint64_t lower_bound_tv(const uint32_t *type, const u
     }
     return lo;
 }
-// first index in [lo,hi) whose key is > key
 __device__ __forceinline__ uint64_t upper_bound_tv(const uint32_t *type, const uint32_t *val, uint64_t lo, uint64_t hi,
                                                    uint64_t key) {
     while (lo < hi) {
@@ -64,22 +148,24 @@ __device__ __forceinline__ uint64_t upper_bound_tv(const uint32_t *type, const u
     return lo;
 }
 
-// max_len < 0: no limit.  connected: count / emit start edges instead of (start,end) pairs.
+// counts are ADDED to counts[q]; hits are written after the genome-part hits (offsets[q] + gcount[q])
 template <bool FILL>
-__global__ void __launch_bounds__(256) query_kernel(GraphView G, const uint64_t *__restrict__ qa,
-                                                    const uint64_t *__restrict__ qb, uint64_t n_q, int64_t max_len,
-                                                    int connected, uint32_t *__restrict__ counts,
-                                                    const uint64_t *__restrict__ offsets, pdg_hit *__restrict__ hits) {
+__global__ void __launch_bounds__(256) xquery_kernel(XView G, const uint64_t *__restrict__ qa,
+                                                     const uint64_t *__restrict__ qb, uint64_t n_q, int64_t max_len,
+                                                     int connected, uint32_t *__restrict__ counts,
+                                                     const uint32_t *__restrict__ gcount,
+                                                     const uint64_t *__restrict__ offsets, pdg_hit *__restrict__ hits) {
     const uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (q >= n_q) return;
-    const int64_t ia = find_node(G, qa[q]);
-    const int64_t ib = find_node(G, qb[q]);
+    const NodeLookup L{nullptr, nullptr, G.codes, G.n_nodes, 0};
+    const int64_t ia = find_code(L, qa[q]);
+    const int64_t ib = find_code(L, qb[q]);
     uint64_t total = 0;
     if (ia >= 0 && ib >= 0) {
         const uint64_t o0 = G.row_ptr[ia], o1 = G.row_ptr[ia + 1];
         const uint64_t i0 = G.col_ptr[ib], i1 = G.col_ptr[ib + 1];
-        uint64_t out_base = FILL ? offsets[q] : 0;
+        uint64_t out_base = FILL ? offsets[q] + gcount[q] : 0;
         if (i1 > i0) {
             for (uint64_t base = o0; base < o1; base += 32) {
                 const uint64_t e = base + lane;
@@ -97,22 +183,16 @@ __global__ void __launch_bounds__(256) query_kernel(GraphView G, const uint64_t 
                     cnt = hi - lo;
                     if (connected) cnt = cnt ? 1 : 0;
                 }
-                // warp exclusive scan of cnt
-                uint64_t inc = cnt;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const uint64_t t = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += t;
-                }
-                const uint64_t wtot = __shfl_sync(0xffffffffu, inc, 31);
+                uint64_t wtot;
+                const uint64_t excl = warp_excl_scan(cnt, lane, &wtot);
                 if (FILL && cnt) {
-                    pdg_hit *dst = hits + out_base + (inc - cnt);
+                    pdg_hit *dst = hits + out_base + excl;
                     for (uint64_t t = 0; t < cnt; ++t) {
                         pdg_hit h;
                         h.type_id = ty;
                         h.i = (int32_t)(vb ^ 0x80000000u);
                         h.j = connected ? h.i : (int32_t)(G.csc_val[lo + t] ^ 0x80000000u);
-                        h.src_tgt_id = G.csr_tgt[e];
+                        h.aux = PDG_HIT_EXPLICIT | G.csr_tgt[e];
                         dst[t] = h;
                     }
                 }
@@ -121,7 +201,7 @@ __global__ void __launch_bounds__(256) query_kernel(GraphView G, const uint64_t 
             }
         }
     }
-    if (!FILL && lane == 0) counts[q] = (uint32_t)min(total, (uint64_t)0xFFFFFFFFu);
+    if (!FILL && lane == 0) counts[q] = (uint32_t)min((uint64_t)counts[q] + total, (uint64_t)0xFFFFFFFFu);
 }
 
 int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q, int64_t max_len,
@@ -142,14 +222,27 @@ int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n
     g->q_a.reserve(n_q * 8, s);
     g->q_b.reserve(n_q * 8, s);
     g->q_cnt.reserve(n_q * 4, s);
+    g->q_cnt_g.reserve(n_q * 4, s);
     PDG_CUDA(cudaMemcpyAsync(g->q_a.p, h_a, n_q * 8, cudaMemcpyHostToDevice, s));
     PDG_CUDA(cudaMemcpyAsync(g->q_b.p, h_b, n_q * 8, cudaMemcpyHostToDevice, s));
-    const GraphView G = view_of(g);
+    const uint64_t *qa = g->q_a.as<uint64_t>(), *qb = g->q_b.as<uint64_t>();
+    uint32_t *cnt = g->q_cnt.as<uint32_t>(), *cnt_g = g->q_cnt_g.as<uint32_t>();
+    const int conn = connected_only ? 1 : 0;
+    const bool has_g = g->g_kmers != 0, has_x = g->x_n_edges != 0;
+    const XView X = xview_of(g);
+    const GView G = gview_of(g);
     const unsigned grid = (unsigned)((n_q * 32 + 255) / 256);
-    query_kernel<false><<<grid, 256, 0, s>>>(G, g->q_a.as<uint64_t>(), g->q_b.as<uint64_t>(), n_q, max_len,
-                                             connected_only ? 1 : 0, g->q_cnt.as<uint32_t>(), nullptr, nullptr);
-    PDG_LAUNCH_CHECK();
-    exclusive_scan_u32_u64(g->q_cnt.as<uint32_t>(), g->q_off.as<uint64_t>(), n_q, g);
+    PDG_CUDA(cudaMemsetAsync(cnt, 0, n_q * 4, s));
+    if (has_g) {
+        gquery_kernel<false><<<grid, 256, 0, s>>>(G, qa, qb, n_q, max_len, conn, cnt, nullptr, nullptr);
+        PDG_LAUNCHED(g);
+    }
+    PDG_CUDA(cudaMemcpyAsync(cnt_g, cnt, n_q * 4, cudaMemcpyDeviceToDevice, s));
+    if (has_x) {
+        xquery_kernel<false><<<grid, 256, 0, s>>>(X, qa, qb, n_q, max_len, conn, cnt, cnt_g, nullptr, nullptr);
+        PDG_LAUNCHED(g);
+    }
+    exclusive_scan_u32_u64(cnt, g->q_off.as<uint64_t>(), n_q, g);
     uint64_t tot = 0;
     PDG_CUDA(cudaMemcpyAsync(&tot, g->q_off.as<uint64_t>() + n_q, 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
@@ -157,26 +250,30 @@ int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n
     *total = tot;
     if (tot) {
         g->q_hits.reserve(tot * sizeof(pdg_hit), s);
-        query_kernel<true><<<grid, 256, 0, s>>>(G, g->q_a.as<uint64_t>(), g->q_b.as<uint64_t>(), n_q, max_len,
-                                                connected_only ? 1 : 0, nullptr, g->q_off.as<uint64_t>(),
-                                                g->q_hits.as<pdg_hit>());
-        PDG_LAUNCH_CHECK();
+        if (has_g) {
+            gquery_kernel<true><<<grid, 256, 0, s>>>(G, qa, qb, n_q, max_len, conn, nullptr, g->q_off.as<uint64_t>(),
+                                                     g->q_hits.as<pdg_hit>());
+            PDG_LAUNCHED(g);
+        }
+        if (has_x) {
+            xquery_kernel<true><<<grid, 256, 0, s>>>(X, qa, qb, n_q, max_len, conn, nullptr, cnt_g,
+                                                     g->q_off.as<uint64_t>(), g->q_hits.as<pdg_hit>());
+            PDG_LAUNCHED(g);
+        }
     }
     return PDG_OK;
 }
 
-// Follows the chain of edges (type, i), (type, i+1) ... (type, j) from the start edge's target
-// (lemon_graph.py:244-264).  status: 0 ok, 1 chain broken, 2 more than one edge (type, m) leaves
-// a node on the chain (the reference's `assert len(chains) == 1` would fire).
-__global__ void walk_kernel(GraphView G, uint64_t src_code, pdg_hit hit, uint32_t *__restrict__ ids,
-                            int32_t *__restrict__ status) {
+// Explicit part: follows the chain of edges (type, i), (type, i+1) ... (type, j) from the start
+// edge's target (lemon_graph.py:244-264).  status: 0 ok, 1 chain broken, 2 more than one edge
+// (type, m) leaves a node on the chain (the reference's `assert len(chains) == 1` would fire).
+__global__ void xwalk_kernel(XView G, uint64_t src_code, pdg_hit hit, uint64_t *__restrict__ codes,
+                             int32_t *__restrict__ status) {
     if (threadIdx.x || blockIdx.x) return;
     int32_t st = 0;
-    const int64_t ia = find_node(G, src_code);
-    if (ia < 0) { *status = 1; return; }
-    ids[0] = (uint32_t)ia;
-    uint32_t cur = hit.src_tgt_id;
-    ids[1] = cur;
+    codes[0] = src_code;
+    uint32_t cur = hit.aux & ~PDG_HIT_EXPLICIT;
+    codes[1] = G.codes[cur];
     uint32_t n = 2;
     for (int64_t m = (int64_t)hit.i + 1; m <= (int64_t)hit.j; ++m) {
         const uint64_t r0 = G.row_ptr[cur], r1 = G.row_ptr[cur + 1];
@@ -185,12 +282,12 @@ __global__ void walk_kernel(GraphView G, uint64_t src_code, pdg_hit hit, uint32_
         if (e >= r1 || tv_key(G.csr_type, G.csr_val, e) != key) { st = 1; break; }
         if (e + 1 < r1 && tv_key(G.csr_type, G.csr_val, e + 1) == key) st = 2;
         cur = G.csr_tgt[e];
-        ids[n++] = cur;
+        codes[n++] = G.codes[cur];
     }
     *status = st;
 }
 
-int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint32_t *h_ids, int32_t *status) {
+int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_codes, int32_t *status) {
     cudaStream_t s = g->stream;
     if (!g->finalized) {
         set_error("query before pdg_finalize");
@@ -201,13 +298,29 @@ int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint32_t *h_
         return PDG_E_INVALID;
     }
     const uint64_t n = (uint64_t)((int64_t)hit->j - (int64_t)hit->i) + 2;
-    g->small.reserve(n * 4 + 16, s);
-    uint32_t *d_ids = g->small.as<uint32_t>() + 4;
+    g->small.reserve(n * 8 + 16, s);
+    uint64_t *d_codes = g->small.as<uint64_t>() + 2;
     int32_t *d_st = g->small.as<int32_t>();
-    PDG_CUDA(cudaMemsetAsync(g->small.p, 0, n * 4 + 16, s));
-    walk_kernel<<<1, 32, 0, s>>>(view_of(g), src_code, *hit, d_ids, d_st);
-    PDG_LAUNCH_CHECK();
-    PDG_CUDA(cudaMemcpyAsync(h_ids, d_ids, n * 4, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaMemsetAsync(g->small.p, 0, n * 8 + 16, s));
+    if (hit->aux & PDG_HIT_EXPLICIT) {
+        if ((hit->aux & ~PDG_HIT_EXPLICIT) >= g->x_n_nodes) {
+            set_error("pdg_query_walk: bad hit");
+            return PDG_E_INVALID;
+        }
+        xwalk_kernel<<<1, 32, 0, s>>>(xview_of(g), src_code, *hit, d_codes, d_st);
+        PDG_LAUNCHED(g);
+    } else {
+        // genome part: the path is the contig slice starting at begin + i (lemon_graph.py:244-264
+        // follows exactly these edges because (type, value) is unique inside G)
+        if (hit->aux >= g->g_begin.size() || hit->i < 0 ||
+            (uint64_t)hit->j + 1 + g->k >= g->g_len[hit->aux] + 1) {
+            set_error("pdg_query_walk: bad hit");
+            return PDG_E_INVALID;
+        }
+        const int rc = emit_codes(g, g->g_begin[hit->aux] + (uint64_t)hit->i, n + g->k - 1, d_codes);
+        if (rc != PDG_OK) return rc;
+    }
+    PDG_CUDA(cudaMemcpyAsync(h_codes, d_codes, n * 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaMemcpyAsync(status, d_st, 4, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
     return PDG_OK;

@@ -191,7 +191,7 @@ static Rec *radix_sort_impl(pdg_graph *g, Rec *a, Rec *b, uint64_t n, const std:
     PDG_CUDA(cudaMemsetAsync(d_hist, 0, hist_bytes, s));
     unsigned hist_grid = (unsigned)std::min<uint64_t>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
     radix_hist_kernel<Rec><<<hist_grid, RS_THREADS, 0, s>>>(a, n, pl, d_hist);
-    PDG_LAUNCH_CHECK();
+    PDG_LAUNCHED(g);
     std::vector<uint64_t> h_hist((size_t)np * 256), h_base((size_t)np * 256);
     PDG_CUDA(cudaMemcpyAsync(h_hist.data(), d_hist, hist_bytes, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
@@ -217,39 +217,29 @@ static Rec *radix_sort_impl(pdg_graph *g, Rec *a, Rec *b, uint64_t n, const std:
     }
     const size_t status_bytes = n_tiles * 256 * sizeof(unsigned long long);
     g->status.reserve(status_bytes, s);
-    std::vector<cudaEvent_t> ev;
+    const bool timed = g->collect_sort_stats;
+    if (timed && !g->ev0) {
+        PDG_CUDA(cudaEventCreate(&g->ev0));
+        PDG_CUDA(cudaEventCreate(&g->ev1));
+    }
     Rec *src = a, *dst = b;
+    if (timed && !run.empty()) PDG_CUDA(cudaEventRecord(g->ev0, s));
     for (int p : run) {
         PDG_CUDA(cudaMemsetAsync(g->status.p, 0, status_bytes, s));
         PDG_CUDA(cudaMemsetAsync(d_ticket, 0, sizeof(unsigned int), s));
-        cudaEvent_t e0, e1;
-        PDG_CUDA(cudaEventCreate(&e0));
-        PDG_CUDA(cudaEventCreate(&e1));
-        PDG_CUDA(cudaEventRecord(e0, s));
         onesweep_kernel<Rec><<<(unsigned)n_tiles, RS_THREADS, smem, s>>>(
             src, dst, n, pl.field[p], pl.shift[p], d_base + (size_t)p * 256,
             g->status.as<unsigned long long>(), d_ticket);
-        PDG_LAUNCH_CHECK();
-        PDG_CUDA(cudaEventRecord(e1, s));
-        ev.push_back(e0);
-        ev.push_back(e1);
+        PDG_LAUNCHED(g);
         std::swap(src, dst);
     }
-    if (!ev.empty()) {
-        PDG_CUDA(cudaStreamSynchronize(s));
-        for (size_t i = 0; i < ev.size(); i += 2) {
-            float ms = 0;
-            cudaEventElapsedTime(&ms, ev[i], ev[i + 1]);
-            if (sizeof(Rec) == 16) {
-                // running average over the edge-record passes of this finalize
-                g->stats.ms_onesweep_avg =
-                    (g->stats.ms_onesweep_avg * g->stats.onesweep_launches + ms) / (g->stats.onesweep_launches + 1);
-                g->stats.onesweep_launches += 1;
-                g->stats.onesweep_records = n;
-            }
-            cudaEventDestroy(ev[i]);
-            cudaEventDestroy(ev[i + 1]);
-        }
+    if (timed && !run.empty()) {
+        PDG_CUDA(cudaEventRecord(g->ev1, s));
+        PDG_CUDA(cudaEventSynchronize(g->ev1));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, g->ev0, g->ev1);
+        g->stats.ms_sort_kernel_avg = ms / (float)run.size();   // includes the status memsets
+        g->stats.sort_kernel_launches = run.size();
     }
     if (passes_run) *passes_run = run.size();
     return src;
@@ -260,10 +250,10 @@ EdgeRec *radix_sort_records(pdg_graph *g, EdgeRec *a, EdgeRec *b, uint64_t n,
     return radix_sort_impl<EdgeRec>(g, a, b, n, passes, passes_run);
 }
 
-uint64_t *radix_sort_keys(pdg_graph *g, uint64_t *a, uint64_t *b, uint64_t n, int key_bits,
+uint64_t *radix_sort_keys(pdg_graph *g, uint64_t *a, uint64_t *b, uint64_t n, int lo_bit, int hi_bit,
                           uint64_t *passes_run) {
     std::vector<PassDesc> passes;
-    for (int sft = 0; sft < key_bits; sft += 8) passes.push_back(PassDesc{0, sft});
+    for (int sft = lo_bit; sft < hi_bit; sft += 8) passes.push_back(PassDesc{0, sft});
     return radix_sort_impl<uint64_t>(g, a, b, n, passes, passes_run);
 }
 

@@ -79,11 +79,11 @@ static void scan_impl(const uint32_t *d_in, OutT *d_out, uint64_t n, pdg_graph *
     g->scratch2.reserve((n_tiles + 1) * sizeof(uint64_t), s);
     uint64_t *tiles = g->scratch2.as<uint64_t>();
     scan_tile_sums<<<(unsigned)n_tiles, SCAN_THREADS, 0, s>>>(d_in, tiles, n);
-    PDG_LAUNCH_CHECK();
+    PDG_LAUNCHED(g);
     scan_tile_offsets<<<1, 1024, 0, s>>>(tiles, n_tiles);
-    PDG_LAUNCH_CHECK();
+    PDG_LAUNCHED(g);
     scan_apply<OutT><<<(unsigned)n_tiles, SCAN_THREADS, 0, s>>>(d_in, d_out, tiles, n, n_tiles);
-    PDG_LAUNCH_CHECK();
+    PDG_LAUNCHED(g);
 }
 
 void exclusive_scan_u32_u64(const uint32_t *d_in, uint64_t *d_out, uint64_t n, pdg_graph *g) {
