@@ -49,7 +49,7 @@ class Hit(ctypes.Structure):
 class BuildStats(ctypes.Structure):
     _fields_ = [("n_residues", c_u64), ("n_contigs", c_u64), ("n_kmers", c_u64),
                 ("n_edge_records", c_u64), ("n_nodes", c_u64), ("n_edges", c_u64),
-                ("node_path", c_u64), ("general_sort", c_u64),
+                ("node_path", c_u64), ("n_demoted", c_u64),
                 ("sort_passes", c_u64), ("sort_records", c_u64),
                 ("ms_upload", ctypes.c_float), ("ms_nodes", ctypes.c_float),
                 ("ms_sort", ctypes.c_float), ("ms_rows", ctypes.c_float),
@@ -68,10 +68,10 @@ SIGNATURES = {
     "pdg_set_stream": (c_int, [vp, vp]),
     "pdg_clear": (c_int, [vp]),
     "pdg_ingest_fasta": (c_int, [vp, vp, c_u64, vp, c_u64, ctypes.POINTER(IngestInfo)]),
-    "pdg_ingest_batch": (c_int, [vp, vp, vp, vp, c_u64, vp, c_u64, vp]),
     "pdg_add_contigs": (c_int, [vp, vp, vp, vp, c_u64]),
     "pdg_kmer_stats": (c_int, [vp, vp, vp, c_u64, u64p, u64p]),
     "pdg_emit_codes": (c_int, [vp, c_u64, c_u64, vp]),
+    "pdg_fetch_residues": (c_int, [vp, c_u64, c_u64, vp]),
     "pdg_add_edges_host": (c_int, [vp, vp, vp, vp, vp, c_u64]),
     "pdg_add_nodes_host": (c_int, [vp, vp, c_u64]),
     "pdg_finalize": (c_int, [vp, c_int]),
@@ -79,6 +79,9 @@ SIGNATURES = {
     "pdg_get_build_stats": (c_int, [vp, ctypes.POINTER(BuildStats)]),
     "pdg_export_nodes": (c_int, [vp, vp]),
     "pdg_export_edges": (c_int, [vp, vp, vp, vp, vp]),
+    "pdg_node_ids": (c_int, [vp, vp, c_u64, vp]),
+    "pdg_index_size": (c_int, [vp, u64p, u64p]),
+    "pdg_export_index": (c_int, [vp, vp, vp, vp]),
     "pdg_checksum": (c_int, [vp, u64p, u64p]),
     "pdg_query_connected": (c_int, [vp, vp, vp, c_u64, u64p]),
     "pdg_query_paths": (c_int, [vp, vp, vp, c_u64, c_i64, u64p]),
@@ -86,7 +89,6 @@ SIGNATURES = {
     "pdg_query_walk": (c_int, [vp, c_u64, ctypes.POINTER(Hit), vp, i32p]),
     "pdg_comm_unique_id": (c_int, [vp]),
     "pdg_comm_init": (c_int, [vp, vp, c_int, c_int]),
-    "pdg_comm_exchange_counts": (c_int, [vp, u64p, u64p]),
 }
 
 _lib = None

@@ -1,0 +1,360 @@
+"""B200Graph: the CUDA backend behind prairiedog's Graph plugin API.
+
+Drop-in for LGGraph (prairiedog/lemon_graph.py:23-334): same methods, same return shapes, same
+"not found is empty, not an exception" convention, data becomes visible to connected()/path() at
+save() like a LemonGraph commit.  All graph content lives on the GPU (libpdgpu.so); this class only
+interns strings (edge_type labels, node values that are not clean k-mers) and converts results back
+into Node / Edge objects.  Bulk entry points (add_genome / add_fasta / path_many) move whole
+genomes and query batches in one call; the per-edge methods keep the reference's call-by-call API.
+"""
+import bisect
+import logging
+import os
+import sys
+import typing
+
+import numpy as np
+
+from . import codec, fasta
+from .edge import Edge
+from .engine import Engine, HIT_EXPLICIT
+from .graph import Graph
+from .node import Node, DEFAULT_NODE_TYPE
+
+log = logging.getLogger("prairiedog")
+
+ET_DELIMITER = ' in '          # prairiedog/subgraph_ref.py:17
+_FLUSH_AT = 1 << 16
+
+
+class _File(object):
+    """One bulk-loaded FASTA file: its contigs own the type ids [type_base, type_base + n)."""
+
+    def __init__(self, basename, host, table, type_base, residue_base, seq_begin, seq_len):
+        self.basename, self.host, self.table = basename, host, table
+        self.type_base, self.n = type_base, int(table.shape[0])
+        self.residue_base, self.seq_begin, self.seq_len = residue_base, seq_begin, seq_len
+        self._strings = None
+
+    def strings(self):
+        if self._strings is None:
+            self._strings = [h + ET_DELIMITER + self.basename for h in fasta.header_strings(self.host, self.table)]
+        return self._strings
+
+
+class B200Graph(Graph):
+    def __init__(self, k: int = 11, device: int = 0, path_limit: int = None):
+        self.k = k
+        self.engine = Engine(k, device)
+        # lemon_graph.py:229-236 skips a pair when its length exceeds sys.getrecursionlimit()
+        self.path_limit = sys.getrecursionlimit() if path_limit is None else path_limit
+        self._reset_host()
+
+    def _reset_host(self):
+        self._types = {}            # type id -> edge_type string (explicit / materialised)
+        self._type_ids = {}         # edge_type string -> type id
+        self._next_type = 0
+        self._files = []            # bulk files, ascending type_base
+        self._file_bases = []
+        self._by_basename = {}
+        self._opaque = []           # opaque node values (not clean k-mers)
+        self._opaque_ids = {}
+        self._node_meta = {}        # node key -> (node_type, labels)
+        self._edge_labels = {}      # (src key, tgt key, type id, value) -> labels
+        self._graph_labels = {}
+        self._st_src, self._st_tgt, self._st_type, self._st_val, self._st_nodes = [], [], [], [], []
+        self._unsaved = False
+        self._published = False     # nothing saved yet: queries see an empty graph
+
+    # ------------------------------------------------------------------ interning
+    def _key(self, value, create=True):
+        """Device key of a node value: the k-mer code, or an opaque id with bit 63 set."""
+        code = codec.encode(value, self.k)
+        if code is not None:
+            return code
+        i = self._opaque_ids.get(value)
+        if i is None:
+            if not create:
+                return None
+            i = len(self._opaque)
+            self._opaque.append(value)
+            self._opaque_ids[value] = i
+        return codec.OPAQUE_BIT | i
+
+    def _value(self, key):
+        key = int(key)
+        if key & codec.OPAQUE_BIT:
+            return self._opaque[key & ~codec.OPAQUE_BIT]
+        return codec.decode(key, self.k)
+
+    def _materialise(self, f):
+        for i, s in enumerate(f.strings()):
+            self._types[f.type_base + i] = s
+            self._type_ids.setdefault(s, f.type_base + i)
+
+    def _type_id(self, s):
+        tid = self._type_ids.get(s)
+        if tid is not None:
+            return tid
+        # could be the label of a bulk-loaded contig whose strings were never built
+        pos = s.find(ET_DELIMITER)
+        while pos >= 0:
+            for f in self._by_basename.get(s[pos + len(ET_DELIMITER):], ()):
+                self._materialise(f)
+            pos = s.find(ET_DELIMITER, pos + 1)
+        tid = self._type_ids.get(s)
+        if tid is None:
+            tid = self._next_type
+            self._next_type += 1
+            self._types[tid] = s
+            self._type_ids[s] = tid
+        return tid
+
+    def _type_string(self, tid):
+        tid = int(tid)
+        s = self._types.get(tid)
+        if s is None:
+            f = self._files[bisect.bisect_right(self._file_bases, tid) - 1]
+            s = f.strings()[tid - f.type_base]
+        return s
+
+    # ------------------------------------------------------------------ per-edge API
+    def upsert_node(self, node: Node, echo: bool = True) -> typing.Optional[Node]:
+        """lemon_graph.py:99-113."""
+        key = self._key(node.value)
+        self._st_nodes.append(key)
+        meta = self._node_meta.get(key)
+        if meta is None or node.labels is not None or node.node_type != DEFAULT_NODE_TYPE:
+            labels = dict(meta[1]) if meta and meta[1] else {}
+            if node.labels:
+                labels.update(node.labels)
+            self._node_meta[key] = (node.node_type, labels or None)
+        self._unsaved = True
+        if len(self._st_nodes) >= _FLUSH_AT:
+            self._flush()
+        if echo:
+            return self._make_node(key)
+
+    def add_edge(self, edge: Edge, echo: bool = True) -> typing.Optional[Edge]:
+        """lemon_graph.py:115-128: both endpoints are upserted, the edge is unique on
+        (type, value, src, tgt)."""
+        ks, kt = self._key(edge.src), self._key(edge.tgt)
+        tid = self._type_id(edge.edge_type)
+        val = int(edge.edge_value)
+        if not -(1 << 31) <= val < (1 << 31):
+            raise ValueError("edge_value {} does not fit the 32-bit value column".format(val))
+        self._st_src.append(ks)
+        self._st_tgt.append(kt)
+        self._st_type.append(tid)
+        self._st_val.append(val)
+        if edge.labels:
+            self._edge_labels.setdefault((ks, kt, tid, val), {}).update(edge.labels)
+        self._unsaved = True
+        if len(self._st_src) >= _FLUSH_AT:
+            self._flush()
+        if echo:
+            return Edge(src=ks + 1, tgt=kt + 1, edge_type=edge.edge_type, edge_value=val,
+                        labels=self._edge_labels.get((ks, kt, tid, val)))
+
+    def _flush(self):
+        if self._st_src:
+            self.engine.add_edges(np.array(self._st_src, dtype=np.uint64), np.array(self._st_tgt, dtype=np.uint64),
+                                  np.array(self._st_type, dtype=np.uint32), np.array(self._st_val, dtype=np.int32))
+            self._st_src, self._st_tgt, self._st_type, self._st_val = [], [], [], []
+        if self._st_nodes:
+            self.engine.add_nodes(np.array(self._st_nodes, dtype=np.uint64))
+            self._st_nodes = []
+
+    def save(self, f: str = None):
+        """lemon_graph.py:154-157: commit.  Everything added so far becomes visible to queries."""
+        self._flush()
+        self.engine.finalize()
+        self._unsaved = False
+        self._published = True
+
+    def _publish(self):
+        if self._unsaved:
+            self.save()
+
+    def clear(self):
+        self.engine.clear()
+        self._reset_host()
+
+    # ------------------------------------------------------------------ bulk API
+    def add_fasta_bytes(self, name, host_bytes) -> int:
+        """Loads one FASTA image (uint8 numpy array / bytes) whose edge labels use ``name`` as the
+        file name.  Returns the number of k-mers it contributes (what update_graph returns,
+        subgraph_ref.py:115).  Raises ValueError for inputs the bulk path cannot represent
+        exactly; SubgraphRef.update_graph then uses the per-edge API instead."""
+        host = np.frombuffer(host_bytes, dtype=np.uint8) if not isinstance(host_bytes, np.ndarray) else host_bytes
+        d = self.engine.to_device(host)
+        return self._add_device(name, host, d)
+
+    def add_fasta(self, path) -> int:
+        return self.add_fasta_bytes(os.path.basename(path), np.fromfile(path, dtype=np.uint8))
+
+    def add_genome(self, km) -> int:
+        """Bulk form of SubgraphRef.update_graph(km, ...) for a well-formed Kmers object."""
+        if km.k != self.k:
+            raise ValueError("Kmers k={} but graph k={}".format(km.k, self.k))
+        if not km.well_formed:
+            raise ValueError("{} needs the per-edge path".format(km))
+        return self._add_device(str(km), km._host, km._d_bytes)
+
+    def _add_device(self, name, host, d_bytes) -> int:
+        info, table = self.engine.ingest(d_bytes)
+        if int(info.n_dirty) != 0 or not int(info.appended):
+            raise ValueError("{}: {} bytes outside the 2-bit alphabet".format(name, int(info.n_dirty)))
+        lay = fasta.Layout(table, int(info.n_residues))
+        if not lay.benign(self.k):
+            # residues stay in the store but no contig refers to them
+            raise ValueError("{}: irregular FASTA layout needs the per-edge path".format(name))
+        base = int(info.residue_base)
+        f = _File(name, host, table, self._next_type, base, lay.seq_begin, lay.seq_len)
+        type_ids = np.arange(f.type_base, f.type_base + f.n, dtype=np.uint32)
+        self._next_type += f.n
+        if name in self._by_basename or self._dup_headers(host, table):
+            # the same label may occur twice: resolve strings now so that equal labels share an id
+            # (libpdgpu then merges those contigs with set semantics)
+            for other in self._by_basename.get(name, ()):
+                self._materialise(other)
+            for i, s in enumerate(f.strings()):
+                tid = self._type_ids.setdefault(s, f.type_base + i)
+                self._types.setdefault(tid, s)
+                type_ids[i] = tid
+        self._files.append(f)
+        self._file_bases.append(f.type_base)
+        self._by_basename.setdefault(name, []).append(f)
+        self.engine.add_contigs(lay.seq_begin + base, lay.seq_len, type_ids)
+        self._unsaved = True
+        long_ = lay.seq_len > self.k
+        return int((lay.seq_len[long_] - self.k + 1).sum())
+
+    @staticmethod
+    def _dup_headers(host, table):
+        """Cheap test for repeated header lines: distinct (length, byte sum) pairs prove uniqueness."""
+        if table.shape[0] < 2:
+            return False
+        b, e = table[:, 0].astype(np.int64), table[:, 1].astype(np.int64)
+        csum = np.concatenate([[0], np.cumsum(host, dtype=np.int64)])
+        w = np.arange(1, host.size + 1, dtype=np.int64)
+        csum2 = np.concatenate([[0], np.cumsum(host.astype(np.int64) * w)])
+        s1 = csum[e] - csum[b]
+        s2 = (csum2[e] - csum2[b]) - s1 * b
+        sig = np.stack([e - b, s1, s2], axis=1)
+        return np.unique(sig, axis=0).shape[0] != sig.shape[0]
+
+    # ------------------------------------------------------------------ enumeration
+    def _make_node(self, key) -> Node:
+        key = int(key)
+        ntype, labels = self._node_meta.get(key, (DEFAULT_NODE_TYPE, None))
+        return Node(value=self._value(key), node_type=ntype, db_id=key + 1, labels=labels)
+
+    @property
+    def nodes(self) -> typing.Set[Node]:
+        """lemon_graph.py:133-140.  db_id = node key + 1 (for a k-mer: its rank among all 4^k
+        k-mers in 'ATCG' product order, plus one -- the reference's kmer_map fixture)."""
+        self._publish()
+        return set(self._make_node(c) for c in self.engine.export_nodes().tolist())
+
+    @property
+    def edges(self) -> typing.Set[Edge]:
+        """lemon_graph.py:142-149: src / tgt are the numeric db ids of the endpoint nodes."""
+        self._publish()
+        src, tgt, ty, val = self.engine.export_edges()
+        out = set()
+        for s, t, y, v in zip(src.tolist(), tgt.tolist(), ty.tolist(), val.tolist()):
+            out.add(Edge(src=s + 1, tgt=t + 1, edge_type=self._type_string(y), edge_value=v,
+                         labels=self._edge_labels.get((s, t, y, v))))
+        return out
+
+    def canonical(self):
+        """(sorted node values, sorted (src value, tgt value, edge_type, edge_value)) -- the
+        canonical forms of SURVEY.md A.2 used by the parity tests."""
+        self._publish()
+        nodes = sorted(self._value(c) for c in self.engine.export_nodes().tolist())
+        src, tgt, ty, val = self.engine.export_edges()
+        edges = sorted((self._value(s), self._value(t), self._type_string(y), v)
+                       for s, t, y, v in zip(src.tolist(), tgt.tolist(), ty.tolist(), val.tolist()))
+        return nodes, edges
+
+    @property
+    def edgelist(self) -> typing.Generator:
+        self._publish()
+        src, tgt, ty, val = self.engine.export_edges()
+        for s, t, y, v in zip(src.tolist(), tgt.tolist(), ty.tolist(), val.tolist()):
+            yield self._value(s), self._value(t), {'edge_type': self._type_string(y), 'edge_value': v}
+
+    def get_labels(self, node: str) -> dict:
+        key = self._key(node, create=False)
+        ntype, labels = self._node_meta.get(key, (DEFAULT_NODE_TYPE, None))
+        d = {'type': ntype, 'value': node}
+        d.update(labels or {})
+        return d
+
+    def set_graph_labels(self, labels: dict):
+        self._graph_labels.update(labels)
+
+    def filter(self):
+        pass
+
+    def __len__(self):
+        self._publish()
+        return self.engine.counts()[0]
+
+    # ------------------------------------------------------------------ queries
+    def _codes(self, values):
+        """Keys of query node values; unknown opaque values map to a key no node has."""
+        missing = codec.OPAQUE_BIT | ((1 << 62) - 1)
+        return np.array([k if (k := self._key(v, create=False)) is not None else missing for v in values],
+                        dtype=np.uint64)
+
+    def connected_many(self, pairs):
+        """Batched connected(): list of (bool, tuple[Edge]) in the order of ``pairs``."""
+        a = self._codes([p[0] for p in pairs])
+        b = self._codes([p[1] for p in pairs])
+        if not self._published:
+            return [(False, ())] * len(pairs)
+        off, hits = self.engine.query_connected(a, b)
+        out = []
+        for q in range(len(pairs)):
+            hs = hits[int(off[q]):int(off[q + 1])]
+            out.append((len(hs) > 0, tuple(self._start_edge(int(a[q]), h) for h in hs)))
+        return out
+
+    def _start_edge(self, src_key, h) -> Edge:
+        tid, i = int(h["type_id"]), int(h["i"])
+        codes, _ = self.engine.walk(src_key, {"type_id": tid, "i": i, "j": i, "aux": h["aux"]})
+        tgt_key = int(codes[1])
+        return Edge(src=src_key + 1, tgt=tgt_key + 1, edge_type=self._type_string(tid), edge_value=i,
+                    labels=self._edge_labels.get((src_key, tgt_key, tid, i)))
+
+    def connected(self, node_a: str, node_b: str) -> typing.Tuple[bool, typing.Tuple]:
+        """lemon_graph.py:178-219."""
+        return self.connected_many([(node_a, node_b)])[0]
+
+    def path_many(self, pairs, limit=None):
+        """Batched path(): list of hit lists [(edge_type, i, j)] -- no Node objects are built."""
+        a = self._codes([p[0] for p in pairs])
+        b = self._codes([p[1] for p in pairs])
+        if not self._published:
+            from .engine import HIT_DTYPE
+            return a, np.zeros(len(pairs) + 1, dtype=np.uint64), np.zeros(0, dtype=HIT_DTYPE)
+        off, hits = self.engine.query_paths(a, b, self.path_limit if limit is None else limit)
+        return a, off, hits
+
+    def path(self, node_a: str, node_b: str) -> typing.Tuple[tuple, tuple]:
+        """lemon_graph.py:275-334."""
+        a, off, hits = self.path_many([(node_a, node_b)])
+        paths, metas = [], []
+        for h in hits:
+            codes, status = self.engine.walk(int(a[0]), h)
+            # lemon_graph.py:254-258: exactly one chain must spell the path
+            assert status == 0, "Length of chains is {} != 1".format(0 if status == 1 else 2)
+            paths.append(tuple(self._make_node(c) for c in codes.tolist()))
+            meta = {'edge_type': self._type_string(h["type_id"])}
+            lab = self._edge_labels.get((int(codes[0]), int(codes[1]), int(h["type_id"]), int(h["i"])))
+            if lab:
+                meta.update(lab)
+            metas.append(meta)
+        return tuple(paths), tuple(metas)

@@ -1,0 +1,189 @@
+"""Engine: one pdg_graph handle of libpdgpu.so with numpy-friendly wrappers.
+
+Host arrays are numpy, device buffers are torch tensors whose ``data_ptr()`` crosses the C ABI
+(include/pdgpu.h).  There is no CPU implementation: constructing an Engine without a CUDA device
+raises PdgError.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _ffi
+from ._ffi import check
+
+HIT_DTYPE = np.dtype([("type_id", np.uint32), ("i", np.int32), ("j", np.int32), ("aux", np.uint32)])
+HIT_EXPLICIT = 0x80000000
+
+
+def _u64(a):
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+class Engine(object):
+    def __init__(self, k=11, device=0):
+        self.lib = _ffi.load()
+        self.k = int(k)
+        self.device = int(device)
+        self.h = self.lib.pdg_create(self.device, self.k)
+        if not self.h:
+            raise _ffi.PdgError(_ffi.PDG_E_CUDA, _ffi.last_error())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.pdg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- ingest ----
+    def to_device(self, host_bytes):
+        """uint8 numpy array / bytes -> torch uint8 CUDA tensor (16-byte aligned by the allocator)."""
+        import torch
+        arr = np.frombuffer(host_bytes, dtype=np.uint8) if not isinstance(host_bytes, np.ndarray) else host_bytes
+        if arr.size == 0:
+            return torch.empty(0, dtype=torch.uint8, device="cuda:%d" % self.device)
+        t = torch.from_numpy(np.ascontiguousarray(arr))
+        return t.to("cuda:%d" % self.device)
+
+    def ingest(self, d_bytes, n_bytes=None):
+        """pdg_ingest_fasta on a CUDA uint8 tensor.  Returns (info, header_table[n_headers,3])."""
+        n = int(d_bytes.numel()) if n_bytes is None else int(n_bytes)
+        info = _ffi.IngestInfo()
+        cap = 1024
+        while True:
+            table = np.zeros((cap, 3), dtype=np.uint64)
+            rc = self.lib.pdg_ingest_fasta(self.h, d_bytes.data_ptr() if n else None, n,
+                                           table.ctypes.data, cap, ctypes.byref(info))
+            if rc == _ffi.PDG_E_CAPACITY:
+                cap = int(info.n_headers)
+                continue
+            check(rc)
+            return info, table[:int(info.n_headers)]
+
+    def add_contigs(self, begin, length, type_id):
+        begin, length = _u64(begin), _u64(length)
+        type_id = np.ascontiguousarray(type_id, dtype=np.uint32)
+        check(self.lib.pdg_add_contigs(self.h, begin.ctypes.data, length.ctypes.data, type_id.ctypes.data,
+                                       begin.size))
+
+    def kmer_stats(self, begin, length):
+        begin, length = _u64(begin), _u64(length)
+        n, u = ctypes.c_uint64(), ctypes.c_uint64()
+        check(self.lib.pdg_kmer_stats(self.h, begin.ctypes.data, length.ctypes.data, begin.size,
+                                      ctypes.byref(n), ctypes.byref(u)))
+        return n.value, u.value
+
+    def fetch_residues(self, begin, length):
+        out = np.zeros(int(length), dtype=np.uint8)
+        check(self.lib.pdg_fetch_residues(self.h, int(begin), int(length), out.ctypes.data))
+        return out.tobytes().decode("ascii")
+
+    def emit_codes(self, begin, length):
+        import torch
+        n = max(int(length) - self.k + 1, 0)
+        d = torch.zeros(max(n, 1), dtype=torch.int64, device="cuda:%d" % self.device)
+        check(self.lib.pdg_emit_codes(self.h, int(begin), int(length), d.data_ptr()))
+        return d[:n].cpu().numpy().view(np.uint64)
+
+    # ---- per-edge API ----
+    def add_edges(self, src, tgt, type_id, value):
+        src, tgt = _u64(src), _u64(tgt)
+        type_id = np.ascontiguousarray(type_id, dtype=np.uint32)
+        value = np.ascontiguousarray(value, dtype=np.int32)
+        check(self.lib.pdg_add_edges_host(self.h, src.ctypes.data, tgt.ctypes.data, type_id.ctypes.data,
+                                          value.ctypes.data, src.size))
+
+    def add_nodes(self, codes):
+        codes = _u64(codes)
+        check(self.lib.pdg_add_nodes_host(self.h, codes.ctypes.data, codes.size))
+
+    # ---- build ----
+    def finalize(self, flags=0):
+        check(self.lib.pdg_finalize(self.h, int(flags)))
+
+    def clear(self):
+        check(self.lib.pdg_clear(self.h))
+
+    def counts(self):
+        a, b, c = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
+        check(self.lib.pdg_counts(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
+        return a.value, b.value, c.value
+
+    def stats(self):
+        st = _ffi.BuildStats()
+        check(self.lib.pdg_get_build_stats(self.h, ctypes.byref(st)))
+        return {f: getattr(st, f) for f, _ in st._fields_ if f != "pad"}
+
+    def export_nodes(self):
+        n = self.counts()[0]
+        out = np.zeros(n, dtype=np.uint64)
+        check(self.lib.pdg_export_nodes(self.h, out.ctypes.data))
+        return out
+
+    def export_edges(self):
+        n = self.counts()[1]
+        src, tgt = np.zeros(n, dtype=np.uint64), np.zeros(n, dtype=np.uint64)
+        ty, val = np.zeros(n, dtype=np.uint32), np.zeros(n, dtype=np.int32)
+        check(self.lib.pdg_export_edges(self.h, src.ctypes.data, tgt.ctypes.data, ty.ctypes.data, val.ctypes.data))
+        return src, tgt, ty, val
+
+    def node_ids(self, codes):
+        codes = _u64(codes)
+        out = np.zeros(codes.size, dtype=np.uint64)
+        check(self.lib.pdg_node_ids(self.h, codes.ctypes.data, codes.size, out.ctypes.data))
+        return out
+
+    def export_index(self):
+        r, p = ctypes.c_uint64(), ctypes.c_uint64()
+        check(self.lib.pdg_index_size(self.h, ctypes.byref(r), ctypes.byref(p)))
+        codes = np.zeros(r.value, dtype=np.uint64)
+        rowptr = np.zeros(r.value + 1, dtype=np.uint32)
+        pos = np.zeros(p.value, dtype=np.uint32)
+        check(self.lib.pdg_export_index(self.h, codes.ctypes.data, rowptr.ctypes.data, pos.ctypes.data))
+        return codes, rowptr, pos
+
+    def checksum(self):
+        a, b = ctypes.c_uint64(), ctypes.c_uint64()
+        check(self.lib.pdg_checksum(self.h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
+    # ---- queries ----
+    def _query(self, fn, a, b, *extra):
+        a, b = _u64(a), _u64(b)
+        tot = ctypes.c_uint64()
+        check(fn(self.h, a.ctypes.data, b.ctypes.data, a.size, *extra, ctypes.byref(tot)))
+        off = np.zeros(a.size + 1, dtype=np.uint64)
+        hits = np.zeros(tot.value, dtype=HIT_DTYPE)
+        check(self.lib.pdg_query_fetch(self.h, off.ctypes.data, hits.ctypes.data if tot.value else None))
+        return off, hits
+
+    def query_connected(self, a, b):
+        """(offsets[n_q+1], hits): one hit per start edge (type_id, i)."""
+        return self._query(self.lib.pdg_query_connected, a, b)
+
+    def query_paths(self, a, b, max_len=-1):
+        """(offsets[n_q+1], hits): one hit per (type_id, i, j) with j - i <= max_len."""
+        return self._query(self.lib.pdg_query_paths, a, b, int(max_len))
+
+    def walk(self, src_code, hit):
+        """Node codes of one hit's path and the chain status (0 ok, 1 broken, 2 ambiguous)."""
+        h = _ffi.Hit(int(hit["type_id"]), int(hit["i"]), int(hit["j"]), int(hit["aux"]))
+        n = int(hit["j"]) - int(hit["i"]) + 2
+        out = np.zeros(n, dtype=np.uint64)
+        st = ctypes.c_int32()
+        check(self.lib.pdg_query_walk(self.h, int(src_code), ctypes.byref(h), out.ctypes.data, ctypes.byref(st)))
+        return out, st.value
+
+    # ---- multi GPU ----
+    def comm_unique_id(self):
+        buf = np.zeros(128, dtype=np.uint8)
+        check(self.lib.pdg_comm_unique_id(buf.ctypes.data))
+        return buf
+
+    def comm_init(self, uid, rank, world):
+        uid = np.ascontiguousarray(uid, dtype=np.uint8)
+        check(self.lib.pdg_comm_init(self.h, uid.ctypes.data, int(rank), int(world)))
