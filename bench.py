@@ -1,0 +1,275 @@
+#!/usr/bin/env python
+"""bench.py -- genome bp/s into the pangenome graph (k=11) on N B200s (BASELINE.json metric).
+
+A step = one pass of the hot path over one batch: FASTA images of G synthetic E. coli-like genomes
+(per rank) -> device parse + 2-bit pack -> k-mer occurrence index (node dedup + labelled edges)
+-> node table of the whole job (NCCL exchange when N > 1).  `value` times it with the FASTA images
+already resident in HBM; `e2e` times the same call path from pinned HOST buffers, host->device
+copies and the device->host read of the result (counts + checksums) inside the timed region.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--genomes G] [--bases B] [--impl reference]
+
+N > 1: launched by torchrun, one rank per GPU (RANK / LOCAL_RANK / WORLD_SIZE from the env).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "genome_bp_per_sec_into_pangenome_graph_k11"
+UNIT = "bp/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--genomes", type=int, default=100, help="genomes per GPU (config 3: 100)")
+    ap.add_argument("--bases", type=int, default=5_000_000)
+    ap.add_argument("--contigs", type=int, default=200)
+    ap.add_argument("--k", type=int, default=11)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-sample-bases", type=int, default=1_500_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(a):
+    return {"workload": "config3: %d synthetic E. coli-like genomes per GPU (%.1f Mbp, %d contigs each), k=%d, "
+                        "one pangenome" % (a.genomes, a.bases / 1e6, a.contigs, a.k),
+            "genomes_per_gpu": a.genomes, "bases_per_genome": a.bases, "contigs_per_genome": a.contigs, "k": a.k,
+            "l2": "inputs (%.0f MB of FASTA per step) exceed the 126 MB L2" % (a.genomes * a.bases * 1.0127 / 1e6)}
+
+
+# ------------------------------------------------------------------ CPU reference arm
+def cpu_reference(a, sample_bases):
+    """Times the reference's own CPU implementation on a bounded sample of the same workload:
+    oracle/_ref/lg_driver (the reference's native LemonGraph engine driven like
+    subgraph_ref.py:51-105) when it was compiled, else the C port oracle/pdg_oracle.c."""
+    from prairiedog_b200 import synth
+    n_gen = max(1, -(-sample_bases // a.bases))
+    tmp = tempfile.mkdtemp(prefix="pdg_cpu_")
+    paths, total = [], 0
+    for name, buf, lens in synth.genomes(n_gen, n_bases=a.bases, n_contigs=a.contigs):
+        p = os.path.join(tmp, name)
+        with open(p, "wb") as f:
+            f.write(buf.tobytes())
+        paths.append(p)
+    drv = os.path.join(ROOT, "oracle", "_ref", "lg_driver")
+    if os.path.exists(drv):
+        db = os.path.join(tmp, "lg.db")
+        out = subprocess.run([drv, db, str(a.k), str(sample_bases)] + paths, capture_output=True, text=True,
+                             timeout=900)
+        rec = json.loads(out.stdout.strip().splitlines()[-1])
+        res = {"value": rec["bp_per_s"], "unit": UNIT, "cores": 1, "kind": "reference",
+               "sample": "%d bp (%d edges) of the same synthetic genomes through the reference's native "
+                         "LemonGraph engine (liblemongraph.so from /root/reference, single writer: 1 process), "
+                         "%.2f s" % (rec["bases"], rec["edges"], rec["seconds"])}
+    else:
+        from oracle.c_oracle import COracle
+        t0 = time.time()
+        o = COracle(a.k)
+        for p in paths:
+            o.add_fasta(p)
+        o.build()
+        dt = time.time() - t0
+        bases = o.counts()[2]
+        res = {"value": bases / dt, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": "%d k-mers through oracle/pdg_oracle.c (sort-based C port), %.2f s" % (bases, dt)}
+    for p in paths:
+        os.remove(p)
+    return res
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals = []
+    for _ in range(a.warmup + a.steps):
+        t0 = time.time()
+        r = cpu_reference(a, a.cpu_sample_bases)
+        vals.append((r, time.time() - t0))
+    timed = vals[a.warmup:]
+    v = sum(r["value"] for r, _ in timed) / len(timed)
+    r = timed[-1][0]
+    r["value"] = v
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": 1e3 * sum(t for _, t in timed) / len(timed),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": workload_config(a), "cpu_baseline": r,
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler(object):
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.p, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.p = None
+
+    def _read(self):
+        for ln in self.p.stdout:
+            self.rows.append(ln.strip())
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ B200 arm
+def run_b200(a):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from prairiedog_b200 import B200Graph, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    g = B200Graph(k=a.k, device=local)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            uid.copy_(torch.from_numpy(g.engine.comm_unique_id()))
+        dist.broadcast(uid, 0)
+        g.engine.comm_init(uid.cpu().numpy(), rank, world)
+
+    # synthetic genomes of this rank: pinned host images and device-resident copies
+    files, n_bases = [], 0
+    for name, buf, lens in synth.genomes(a.genomes, n_bases=a.bases, n_contigs=a.contigs, first=rank * a.genomes):
+        pinned = torch.from_numpy(buf).pin_memory()
+        files.append((name, buf, pinned, pinned.to(dev)))
+        n_bases += int(lens.sum())
+    h2d_bytes = sum(int(f[1].size) for f in files)
+
+    def step(resident):
+        g.clear()
+        for name, host, pinned, d in files:
+            g._add_device(name, host, d if resident else pinned.to(dev, non_blocking=True))
+        g.save()
+        if resident:
+            return g.engine.counts()
+        return g.engine.counts() + g.engine.checksum()      # device -> host read of the result
+
+    def timed(resident, steps, warmup, sampler=None):
+        for _ in range(warmup):
+            step(resident)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = step(resident)
+        e1.record()
+        torch.cuda.synchronize()
+        clocks = sampler.stop() if sampler else None
+        if world > 1:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), out, clocks
+
+    ms, out, clocks = timed(True, a.steps, a.warmup, ClockSampler(local))
+    st = g.engine.stats()
+    ms_e2e, out_e2e, _ = timed(False, max(2, min(a.steps, 3)), 1)
+    total_bases = torch.tensor([float(n_bases)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(total_bases)
+    total_bases = float(total_bases.item())
+
+    if rank == 0:
+        peaks = {}
+        pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(pk):
+            peaks = json.load(open(pk))
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        rec_bytes = 8 if a.k <= 16 else 16
+        alg_bytes = 2.0 * rec_bytes * st["sort_records"]               # one pass: read + write every record
+        t_kernel = st["ms_sort_kernel_avg"] * 1e-3
+        achieved = alg_bytes / t_kernel / 1e9 if t_kernel > 0 else 0.0
+        line = {
+            "metric": METRIC, "value": total_bases / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic", "config": workload_config(a),
+            "e2e": {"value": total_bases / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": 5 * 8 + sum(int(f.table.nbytes) + 48 for f in g._files), "ms_per_step": ms_e2e},
+            "gpu_launches": int(st["kernel_launches"]) * a.steps,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "onesweep_kernel (one LSD partition pass of the occurrence index)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                         "traffic": None, "launches_per_step": int(st["sort_kernel_launches"]),
+                         "records_per_launch": int(st["sort_records"]), "ms_per_launch": st["ms_sort_kernel_avg"]},
+            "result": {"n_nodes": int(out[0]), "n_edges_rank0": int(out[1]), "n_kmers_rank0": int(out[2]),
+                       "checksums_rank0": [int(x) for x in out_e2e[3:]]},
+            "phases_ms": {k: st[k] for k in ("ms_upload", "ms_sort", "ms_explicit", "ms_nodes", "ms_total")},
+        }
+        if world == 1 and not a.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_reference(a, a.cpu_sample_bases)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

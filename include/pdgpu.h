@@ -93,7 +93,7 @@ typedef struct pdg_build_stats {
     float ms_sort_kernel_avg;   /* CUDA-event average of one partition pass kernel */
     float pad;
     uint64_t sort_kernel_launches;
-    uint64_t kernel_launches;   /* kernels launched by the last pdg_finalize */
+    uint64_t kernel_launches;   /* kernels launched on this handle since pdg_create / pdg_clear */
 } pdg_build_stats;
 
 const char *pdg_last_error(void);

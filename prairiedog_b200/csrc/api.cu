@@ -90,6 +90,7 @@ int pdg_clear(pdg_graph *g) {
     g->g_kmers = g->g_edges = g->g_nodes = 0;
     g->x_n_nodes = g->x_n_edges = 0;
     g->q_n = g->q_total = 0;
+    g->launches = 0;
     return PDG_OK;
     PDG_API_END
 }
@@ -188,6 +189,7 @@ int pdg_counts(pdg_graph *g, uint64_t *n_nodes, uint64_t *n_edges, uint64_t *n_k
 int pdg_get_build_stats(pdg_graph *g, pdg_build_stats *out) {
     PDG_API_BEGIN
     *out = g->stats;
+    out->kernel_launches = g->launches;
     return PDG_OK;
     PDG_API_END
 }

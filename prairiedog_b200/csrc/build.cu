@@ -32,7 +32,6 @@ int finalize(pdg_graph *g, int flags) {
     cudaStream_t s = g->stream;
     Timer total(s), lap(s);
     g->stats = pdg_build_stats{};
-    g->launches = 0;
     g->finalized = false;
     const int k = g->k;
     if (g->n_res >= (1ULL << 32)) {

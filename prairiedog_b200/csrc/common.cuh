@@ -111,7 +111,7 @@ struct pdg_graph {
     int device = 0;
     int k = 11;
     cudaStream_t stream = nullptr;
-    uint64_t launches = 0;         // kernels launched (reset by pdg_finalize)
+    uint64_t launches = 0;         // kernels launched since pdg_create / pdg_clear
 
     // ---- genome store: residues packed 2 bits each, big endian inside 64-bit words ----
     pdg::DevBuf packed;            // uint64 words, zero beyond n_res
