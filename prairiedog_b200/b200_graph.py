@@ -57,6 +57,7 @@ class B200Graph(Graph):
         self._files = []            # bulk files, ascending type_base
         self._file_bases = []
         self._by_basename = {}
+        self._explicit_suffixes = set()   # every text after an ' in ' of an explicit edge_type
         self._opaque = []           # opaque node values (not clean k-mers)
         self._opaque_ids = {}
         self._node_meta = {}        # node key -> (node_type, labels)
@@ -108,6 +109,10 @@ class B200Graph(Graph):
             self._next_type += 1
             self._types[tid] = s
             self._type_ids[s] = tid
+            pos = s.find(ET_DELIMITER)
+            while pos >= 0:      # a later bulk load of a file with this name must compare labels
+                self._explicit_suffixes.add(s[pos + len(ET_DELIMITER):])
+                pos = s.find(ET_DELIMITER, pos + 1)
         return tid
 
     def _type_string(self, tid):
@@ -213,7 +218,7 @@ class B200Graph(Graph):
         f = _File(name, host, table, self._next_type, base, lay.seq_begin, lay.seq_len)
         type_ids = np.arange(f.type_base, f.type_base + f.n, dtype=np.uint32)
         self._next_type += f.n
-        if name in self._by_basename or self._dup_headers(host, table):
+        if name in self._by_basename or name in self._explicit_suffixes or self._dup_headers(host, table):
             # the same label may occur twice: resolve strings now so that equal labels share an id
             # (libpdgpu then merges those contigs with set semantics)
             for other in self._by_basename.get(name, ()):
@@ -232,17 +237,14 @@ class B200Graph(Graph):
 
     @staticmethod
     def _dup_headers(host, table):
-        """Cheap test for repeated header lines: distinct (length, byte sum) pairs prove uniqueness."""
+        """True when two header lines of the file are byte-identical."""
         if table.shape[0] < 2:
             return False
-        b, e = table[:, 0].astype(np.int64), table[:, 1].astype(np.int64)
-        csum = np.concatenate([[0], np.cumsum(host, dtype=np.int64)])
-        w = np.arange(1, host.size + 1, dtype=np.int64)
-        csum2 = np.concatenate([[0], np.cumsum(host.astype(np.int64) * w)])
-        s1 = csum[e] - csum[b]
-        s2 = (csum2[e] - csum2[b]) - s1 * b
-        sig = np.stack([e - b, s1, s2], axis=1)
-        return np.unique(sig, axis=0).shape[0] != sig.shape[0]
+        mv = memoryview(host)
+        seen = set()
+        for b, e in table[:, :2].tolist():
+            seen.add(bytes(mv[b:e]))
+        return len(seen) != table.shape[0]
 
     # ------------------------------------------------------------------ enumeration
     def _make_node(self, key) -> Node:
