@@ -5,6 +5,7 @@
 // Reference counterpart: the node_idx / srcnode_idx / tgtnode_idx B-trees that LemonGraph fills
 // one key at a time (lemongraph/lib/lemongraph.c:591-630).
 #include "gindex.cuh"
+#include "msd3.cuh"
 #include <algorithm>
 
 namespace pdg {
@@ -88,13 +89,11 @@ void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, i
     uint64_t passes = 0;
     g->collect_sort_stats = true;
     if (k <= 16) {
-        g->recA.reserve(n * 8, s);
-        g->recB.reserve(n * 8, s);
-        out.codes = g->recA.as<uint64_t>();
-        run_traverse(g, MODE_REC64, ct, hc.pos0, hc.pos1, out);
-        const uint64_t *sorted =
-            radix_sort_keys(g, g->recA.as<uint64_t>(), g->recB.as<uint64_t>(), n, 32, 32 + 2 * k, &passes);
-        rows_from_sorted<uint64_t>(g, sorted, n);
+        // fused path (ksort.cu): the first pass reads the packed genome, the last writes positions
+        const uint64_t *sorted = nullptr;
+        if (2 * k <= kMsd3MaxBits && !(flags & PDG_F_FORCE_SORT_NODES)) msd3_build(g, ct, hc);   // msd3.cu
+        else if (!ksort_build(g, ct, hc, &sorted)) rows_from_sorted<uint64_t>(g, sorted, n);
+        passes = g->stats.sort_passes;
     } else {
         g->recA.reserve(n * 16, s);
         g->recB.reserve(n * 16, s);

@@ -39,6 +39,12 @@ void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, i
 ContigTable g_table(const pdg_graph *g);
 NodeLookup g_lookup(const pdg_graph *g);
 
+// ksort.cu: fused emission + sort for k <= 16; true when rows were built from the direct table
+bool ksort_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, const uint64_t **sorted_out);
+
+// msd3.cu: offsets-first MSD sort for k <= 11 (no look-back)
+void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc);
+
 // xbuild.cu: builds the explicit part from g->x_* plus the demoted contigs
 void build_x_part(pdg_graph *g, const HostContigs &demoted);
 
