@@ -43,46 +43,54 @@ __device__ __forceinline__ bool m3_valid(const ContigTable &ct, const M3Contigs 
 }
 
 // ---- histograms from the packed genome --------------------------------------------------------
-// H1T[d3][tile]; H12[chunk][d3 << b2 | d2]; tot32[cell] += chunk counts
-__global__ void __launch_bounds__(M3_THREADS) m3_hist_kernel(const unsigned long long *__restrict__ packed,
-                                                             uint64_t packed_words, int k, ContigTable ct, M3Plan pl,
-                                                             uint32_t *__restrict__ H1T, uint32_t *__restrict__ H12,
-                                                             unsigned int *__restrict__ tot32) {
+// H1T[d3][tile]; H12[chunk][d3 << b2 | d2]; tot32[cell] += chunk counts.
+// One CTA per chunk; every WARP takes whole tiles on its own (private d3 counters, its own copy of
+// the tile's packed words), so there is no block barrier inside the tile loop.
+static constexpr int M3H_THREADS = 1024;
+static constexpr int M3H_WARPS = M3H_THREADS / 32;
+__global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const unsigned long long *__restrict__ packed,
+                                                              uint64_t packed_words, int k, ContigTable ct, M3Plan pl,
+                                                              uint32_t *__restrict__ H1T, uint32_t *__restrict__ H12,
+                                                              unsigned int *__restrict__ tot32) {
     extern __shared__ uint32_t h12[];   // [cells]
-    __shared__ uint32_t h1[128];
-    __shared__ unsigned long long words[M3_WORDS];
-    __shared__ M3Contigs tc;
-    const int tid = threadIdx.x;
+    __shared__ uint32_t h1[M3H_WARPS][128];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t cells = 1u << (pl.b3 + pl.b2), B3 = 1u << pl.b3;
     const int sh2 = pl.b1, sh3 = pl.b1 + pl.b2;
-    for (uint32_t i = tid; i < cells; i += M3_THREADS) h12[i] = 0;
+    for (uint32_t i = tid; i < cells; i += M3H_THREADS) h12[i] = 0;
+    __syncthreads();
     const uint32_t t0 = blockIdx.x * pl.ch, t1 = min(t0 + pl.ch, pl.n_tiles);
-    for (uint32_t tile = t0; tile < t1; ++tile) {
+    for (uint32_t tile = t0 + w; tile < t1; tile += M3H_WARPS) {
         const uint64_t p0 = pl.pos0 + (uint64_t)tile * M3_TILE, p1 = min(p0 + (uint64_t)M3_TILE, pl.pos1);
-        __syncthreads();
-        for (int i = tid; i < M3_WORDS; i += M3_THREADS) {
-            const uint64_t wi = (p0 >> 5) + i;
-            words[i] = wi < packed_words ? packed[wi] : 0ULL;
-        }
-        if (tid < 128) h1[tid] = 0;
-        if (tid == 0) m3_tile_contigs(ct, p0, p1, k, &tc);
-        __syncthreads();
+        for (int i = lane; i < 128; i += 32) h1[w][i] = 0;
+        M3Contigs tc;
+        m3_tile_contigs(ct, p0, p1, k, &tc);
+        __syncwarp();
+        // lane l walks positions p0 + 32*i + l: the window starts in word (p >> 5) and may spill
+        // into the next one, so keep a sliding pair of words
+        const uint64_t w0 = p0 >> 5;
         const uint32_t lead = (uint32_t)(p0 & 31u);
-#pragma unroll 4
-        for (int j = 0; j < M3_ITEMS; ++j) {
-            const uint32_t l = j * M3_THREADS + tid;
-            const uint64_t p = p0 + l;
+        const uint32_t n_steps = (uint32_t)((p1 - p0 + 31) >> 5);
+        for (uint32_t i = 0; i < n_steps; ++i) {
+            const uint64_t q = (uint64_t)lead + 32u * i + lane;       // slot relative to word w0
+            const uint64_t p = p0 + 32u * i + lane;
+            const uint64_t wi = w0 + (q >> 5);
+            const unsigned long long hi = wi < packed_words ? packed[wi] : 0ULL;
+            const unsigned long long lo = wi + 1 < packed_words ? packed[wi + 1] : 0ULL;
+            const uint32_t sft = 2u * (uint32_t)(q & 31u);
+            const unsigned long long x = sft ? ((hi << sft) | (lo >> (64 - sft))) : hi;
+            const uint32_t code = (uint32_t)(x >> (64 - 2 * k));
             if (p < p1 && m3_valid(ct, tc, p, k)) {
-                const uint32_t code = (uint32_t)kmer_at(words, lead + l, k);
-                atomicAdd(&h1[code >> sh3], 1u);
+                atomicAdd(&h1[w][code >> sh3], 1u);
                 atomicAdd(&h12[code >> sh2], 1u);
             }
         }
-        __syncthreads();
-        if (tid < (int)B3) H1T[(size_t)tid * pl.n_tiles + tile] = h1[tid];
+        __syncwarp();
+        for (uint32_t i = lane; i < B3; i += 32) H1T[(size_t)i * pl.n_tiles + tile] = h1[w][i];
+        __syncwarp();
     }
     __syncthreads();
-    for (uint32_t i = tid; i < cells; i += M3_THREADS) {
+    for (uint32_t i = tid; i < cells; i += M3H_THREADS) {
         const uint32_t v = h12[i];
         H12[(size_t)blockIdx.x * cells + i] = v;
         if (v) atomicAdd(&tot32[i], v);
@@ -125,10 +133,16 @@ __global__ void __launch_bounds__(256) m3_scan_chunks_kernel(uint32_t *__restric
     const uint32_t cell = blockIdx.x * 256 + threadIdx.x;
     if (cell >= cells) return;
     uint32_t run = base32[cell];
-    for (uint32_t c = 0; c < n_chunks; ++c) {
-        const uint32_t v = H12[(size_t)c * cells + cell];
-        H12[(size_t)c * cells + cell] = run;
-        run += v;
+    constexpr int U = 16;   // independent loads in flight
+    for (uint32_t c0 = 0; c0 < n_chunks; c0 += U) {
+        uint32_t v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) v[u] = c0 + u < n_chunks ? H12[(size_t)(c0 + u) * cells + cell] : 0u;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (c0 + u < n_chunks) H12[(size_t)(c0 + u) * cells + cell] = run;
+            run += v[u];
+        }
     }
 }
 
@@ -305,7 +319,7 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     }
     const unsigned long long *packed = g->packed.as<unsigned long long>();
     const uint64_t pw = g->packed.cap / 8;
-    m3_hist_kernel<<<pl.n_chunks, M3_THREADS, cells * 4, s>>>(packed, pw, k, ct, pl, H1T, H12, tot32);
+    m3_hist_kernel<<<pl.n_chunks, M3H_THREADS, cells * 4, s>>>(packed, pw, k, ct, pl, H1T, H12, tot32);
     PDG_LAUNCHED(g);
     m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32);
     PDG_LAUNCHED(g);
