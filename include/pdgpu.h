@@ -48,7 +48,7 @@
 extern "C" {
 #endif
 
-#define PDG_ABI_VERSION 2
+#define PDG_ABI_VERSION 3
 
 #define PDG_OK            0
 #define PDG_E_INVALID    -1   /* bad argument / bad state */
@@ -94,10 +94,21 @@ typedef struct pdg_build_stats {
     float pad;
     uint64_t sort_kernel_launches;
     uint64_t kernel_launches;   /* kernels launched on this handle since pdg_create / pdg_clear */
+    /* CUDA-event times of the k <= 11 index build (msd3.cu): joint histogram, offset scans, and
+     * the three partition passes; 0 when another path ran */
+    float ms_hist, ms_scans, ms_pass[3], pad2;
+    /* CUDA-event times of the last pdg_ingest_fasta_batch: pass A (summaries; in host mode it
+     * includes waiting for the copies), pass B (scan), pass C (emit + header hashes) */
+    float ms_ingest_a, ms_ingest_b, ms_ingest_c, pad3;
+    uint64_t ingest_bytes;      /* bytes parsed by the last pdg_ingest_fasta_batch */
+    uint64_t ingest_launches;
 } pdg_build_stats;
 
 const char *pdg_last_error(void);
 int pdg_abi_version(void);
+/* sizeof(pdg_hit), sizeof(pdg_ingest_info), sizeof(pdg_build_stats) as compiled into the library,
+ * so that a binding can verify its struct mirrors (needs no device) */
+int pdg_struct_sizes(uint64_t *hit, uint64_t *ingest_info, uint64_t *build_stats);
 
 /* lifetime.  Replaces LGGraph.__init__ / clear (lemon_graph.py:27-42,130-131). */
 pdg_graph *pdg_create(int device, int k);
@@ -114,6 +125,22 @@ int pdg_clear(pdg_graph *g);
  * pdg_add_edges_host). */
 int pdg_ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes,
                      uint64_t *h_header_table, uint64_t cap_headers, pdg_ingest_info *info);
+
+/* Batched pdg_ingest_fasta: n_files images in one call (three launches for the whole batch instead
+ * of three per file), with the same results as calling pdg_ingest_fasta on every file in order --
+ * same residue_base / n_residues / n_headers / n_dirty per file, same store contents.  ptrs[f] is
+ * a device pointer, or with PDG_IN_HOST a host pointer (pinned memory recommended): the library
+ * then stages the images on the device itself, copying on a second stream while the files that
+ * already arrived are being parsed.  h_header_table receives the rows of all files back to back
+ * (file f's rows start at the sum of infos[0..f).n_headers), FOUR uint64 per row: {byte_begin,
+ * byte_end, residue_index, hash}; hash is a 64-bit hash of the right-stripped header line, or 0
+ * when the host has to compare the bytes itself.  PDG_E_CAPACITY if the table is too small (every
+ * infos[f].n_headers is then valid and nothing was appended).  Replaces the `for` loop over
+ * genome files around Kmers._load (kmers.py:51-77; Snakefile rule kmers). */
+#define PDG_IN_HOST 1
+int pdg_ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t *n_bytes,
+                           uint32_t n_files, int flags, uint64_t *h_header_table,
+                           uint64_t cap_headers, pdg_ingest_info *infos);
 
 /* Declares contigs over residues already in the store: contig c covers residues
  * [h_begin[c], h_begin[c]+h_len[c]) and all its edges carry type id h_type_id[c].  Contigs with

@@ -19,6 +19,7 @@ PDG_E_COMM = -5
 
 PDG_F_FORCE_SORT_NODES = 1
 PDG_F_FORCE_GENERAL = 2
+PDG_IN_HOST = 1
 
 u8p = ctypes.POINTER(ctypes.c_uint8)
 u32p = ctypes.POINTER(ctypes.c_uint32)
@@ -41,6 +42,10 @@ class IngestInfo(ctypes.Structure):
                 ("n_dirty", c_u64), ("residue_base", c_u64), ("appended", c_u64)]
 
 
+INGEST_INFO_DTYPE = [("n_bytes", "<u8"), ("n_headers", "<u8"), ("n_residues", "<u8"),
+                     ("n_dirty", "<u8"), ("residue_base", "<u8"), ("appended", "<u8")]
+
+
 class Hit(ctypes.Structure):
     _fields_ = [("type_id", ctypes.c_uint32), ("i", ctypes.c_int32), ("j", ctypes.c_int32),
                 ("aux", ctypes.c_uint32)]
@@ -55,7 +60,11 @@ class BuildStats(ctypes.Structure):
                 ("ms_sort", ctypes.c_float), ("ms_rows", ctypes.c_float),
                 ("ms_explicit", ctypes.c_float), ("ms_total", ctypes.c_float),
                 ("ms_sort_kernel_avg", ctypes.c_float), ("pad", ctypes.c_float),
-                ("sort_kernel_launches", c_u64), ("kernel_launches", c_u64)]
+                ("sort_kernel_launches", c_u64), ("kernel_launches", c_u64),
+                ("ms_hist", ctypes.c_float), ("ms_scans", ctypes.c_float), ("ms_pass", ctypes.c_float * 3),
+                ("pad2", ctypes.c_float),
+                ("ms_ingest_a", ctypes.c_float), ("ms_ingest_b", ctypes.c_float), ("ms_ingest_c", ctypes.c_float),
+                ("pad3", ctypes.c_float), ("ingest_bytes", c_u64), ("ingest_launches", c_u64)]
 
 
 # name -> (restype, argtypes); every symbol of include/pdgpu.h (tests/test_abi.py checks the list
@@ -63,11 +72,13 @@ class BuildStats(ctypes.Structure):
 SIGNATURES = {
     "pdg_last_error": (ctypes.c_char_p, []),
     "pdg_abi_version": (c_int, []),
+    "pdg_struct_sizes": (c_int, [u64p, u64p, u64p]),
     "pdg_create": (vp, [c_int, c_int]),
     "pdg_destroy": (None, [vp]),
     "pdg_set_stream": (c_int, [vp, vp]),
     "pdg_clear": (c_int, [vp]),
     "pdg_ingest_fasta": (c_int, [vp, vp, c_u64, vp, c_u64, ctypes.POINTER(IngestInfo)]),
+    "pdg_ingest_fasta_batch": (c_int, [vp, vp, vp, ctypes.c_uint32, c_int, vp, c_u64, vp]),
     "pdg_add_contigs": (c_int, [vp, vp, vp, vp, c_u64]),
     "pdg_kmer_stats": (c_int, [vp, vp, vp, c_u64, u64p, u64p]),
     "pdg_emit_codes": (c_int, [vp, c_u64, c_u64, vp]),
@@ -110,8 +121,8 @@ def load(build_if_missing=False):
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    if lib.pdg_abi_version() != 2:
-        raise PdgError(PDG_E_INVALID, "libpdgpu ABI %d, expected 2: rebuild" % lib.pdg_abi_version())
+    if lib.pdg_abi_version() != 3:
+        raise PdgError(PDG_E_INVALID, "libpdgpu ABI %d, expected 3: rebuild" % lib.pdg_abi_version())
     _lib = lib
     return lib
 

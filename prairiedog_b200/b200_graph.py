@@ -208,13 +208,19 @@ class B200Graph(Graph):
 
     def _add_device(self, name, host, d_bytes) -> int:
         info, table = self.engine.ingest(d_bytes)
-        if int(info.n_dirty) != 0 or not int(info.appended):
-            raise ValueError("{}: {} bytes outside the 2-bit alphabet".format(name, int(info.n_dirty)))
-        lay = fasta.Layout(table, int(info.n_residues))
+        return self._register(name, host, int(info.n_dirty), int(info.appended), int(info.n_residues),
+                              int(info.residue_base), table)
+
+    def _register(self, name, host, n_dirty, appended, n_residues, residue_base, table) -> int:
+        """Host bookkeeping of one parsed file: contig layout (kmers.py:61-75), type ids of its
+        edge labels, contig declaration.  table: rows {byte_begin, byte_end, residue_index}."""
+        if n_dirty != 0 or not appended:
+            raise ValueError("{}: {} bytes outside the 2-bit alphabet".format(name, n_dirty))
+        lay = fasta.Layout(table, n_residues)
         if not lay.benign(self.k):
             # residues stay in the store but no contig refers to them
             raise ValueError("{}: irregular FASTA layout needs the per-edge path".format(name))
-        base = int(info.residue_base)
+        base = residue_base
         f = _File(name, host, table, self._next_type, base, lay.seq_begin, lay.seq_len)
         type_ids = np.arange(f.type_base, f.type_base + f.n, dtype=np.uint32)
         self._next_type += f.n
@@ -234,6 +240,79 @@ class B200Graph(Graph):
         self._unsaved = True
         long_ = lay.seq_len > self.k
         return int((lay.seq_len[long_] - self.k + 1).sum())
+
+    def add_fasta_batch(self, files) -> typing.List[int]:
+        """Bulk form of the loop over genome files (Snakefile rule kmers + pangenome): ``files`` is
+        a list of (name, host uint8 array, CUDA uint8 tensor or None).  With device tensors the
+        images are parsed where they are; if any tensor is None the HOST arrays (pinned memory
+        recommended) cross the C ABI and libpdgpu stages them itself, overlapping the copies with
+        the parse.  Returns the k-mer count of every file (subgraph_ref.py:115).  Files the bulk
+        path cannot represent exactly are skipped and reported through a ValueError whose
+        ``failed`` attribute lists their indices (callers route those through the per-edge API)."""
+        if not files:
+            return []
+        names = [f[0] for f in files]
+        hosts = [f[1] if isinstance(f[1], np.ndarray) else np.frombuffer(f[1], dtype=np.uint8) for f in files]
+        devs = [f[2] if len(f) > 2 else None for f in files]
+        use_host = any(d is None for d in devs)
+        if use_host:
+            ptrs = [h.ctypes.data if h.size else 0 for h in hosts]
+        else:
+            ptrs = [d.data_ptr() if d.numel() else 0 for d in devs]
+        infos, table, row_base = self.engine.ingest_batch(ptrs, [h.size for h in hosts], host=use_host)
+        k = self.k
+        n = len(files)
+        nh = infos["n_headers"].astype(np.int64)
+        nres = infos["n_residues"].astype(np.int64)
+        rbase = infos["residue_base"].astype(np.int64)
+        # fast path: every file clean, aligned (a header first, no empty record), every contig
+        # longer than k, labels certainly distinct -> one vectorised pass for the whole batch
+        fast = bool((infos["n_dirty"] == 0).all() and (infos["appended"] == 1).all() and (nh > 0).all()
+                    and len(set(names)) == n
+                    and not any(nm in self._by_basename or nm in self._explicit_suffixes for nm in names))
+        if fast:
+            res = table[:, 2].astype(np.int64)
+            end = np.empty_like(res)
+            end[:-1] = res[1:]
+            end[row_base[1:] - 1] = nres
+            lens = end - res
+            file_of = np.repeat(np.arange(n, dtype=np.int64), nh)
+            hashes = table[:, 3]
+            mixed = hashes ^ (file_of.astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15))
+            fast = bool((res[row_base[:-1]] == 0).all() and (lens > k).all() and (hashes != 0).all()
+                        and np.unique(mixed).size == mixed.size)
+        if fast:
+            type0 = self._next_type
+            counts = []
+            kmers = np.add.reduceat(lens - (k - 1), row_base[:-1])
+            for i in range(n):
+                a, b = int(row_base[i]), int(row_base[i + 1])
+                f = _File(names[i], hosts[i], table[a:b, :3], type0 + a, int(rbase[i]), res[a:b], lens[a:b])
+                self._files.append(f)
+                self._file_bases.append(f.type_base)
+                self._by_basename.setdefault(names[i], []).append(f)
+                counts.append(int(kmers[i]))
+            self._next_type = type0 + int(row_base[-1])
+            self.engine.add_contigs(res + rbase[file_of], lens,
+                                    np.arange(type0, type0 + res.size, dtype=np.uint32))
+            self._unsaved = True
+            return counts
+        counts, failed, msgs = [], [], []
+        for i in range(n):
+            a, b = int(row_base[i]), int(row_base[i + 1])
+            try:
+                counts.append(self._register(names[i], hosts[i], int(infos["n_dirty"][i]), int(infos["appended"][i]),
+                                             int(nres[i]), int(rbase[i]), np.ascontiguousarray(table[a:b, :3])))
+            except ValueError as e:
+                counts.append(0)
+                failed.append(i)
+                msgs.append(str(e))
+        if failed:
+            err = ValueError("; ".join(msgs))
+            err.failed = failed
+            err.counts = counts
+            raise err
+        return counts
 
     @staticmethod
     def _dup_headers(host, table):

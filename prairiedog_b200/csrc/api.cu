@@ -38,6 +38,12 @@ extern "C" {
 
 const char *pdg_last_error(void) { return g_err; }
 int pdg_abi_version(void) { return PDG_ABI_VERSION; }
+int pdg_struct_sizes(uint64_t *hit, uint64_t *ingest_info, uint64_t *build_stats) {
+    if (hit) *hit = sizeof(pdg_hit);
+    if (ingest_info) *ingest_info = sizeof(pdg_ingest_info);
+    if (build_stats) *build_stats = sizeof(pdg_build_stats);
+    return PDG_OK;
+}
 
 pdg_graph *pdg_create(int device, int k) {
     if (k < 1 || k > 31) {
@@ -66,6 +72,14 @@ void pdg_destroy(pdg_graph *g) {
     cudaStreamSynchronize(g->stream);
     if (g->ev0) cudaEventDestroy(g->ev0);
     if (g->ev1) cudaEventDestroy(g->ev1);
+    if (g->fb_ev_ready) cudaEventDestroy(g->fb_ev_ready);
+    for (cudaEvent_t e : g->fb_events) cudaEventDestroy(e);
+    for (cudaEvent_t e : g->k_events) cudaEventDestroy(e);
+    for (cudaEvent_t e : g->i_events) cudaEventDestroy(e);
+    if (g->copy_stream) {
+        cudaStreamSynchronize(g->copy_stream);
+        cudaStreamDestroy(g->copy_stream);
+    }
     delete g;
 }
 
@@ -103,6 +117,17 @@ int pdg_ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes, uin
         return PDG_E_INVALID;
     }
     return ingest_fasta(g, d_bytes, n_bytes, h_header_table, cap_headers, info);
+    PDG_API_END
+}
+
+int pdg_ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t *n_bytes, uint32_t n_files,
+                           int flags, uint64_t *h_header_table, uint64_t cap_headers, pdg_ingest_info *infos) {
+    PDG_API_BEGIN
+    if (n_files && (!ptrs || !n_bytes || !infos)) {
+        set_error("pdg_ingest_fasta_batch: null argument");
+        return PDG_E_INVALID;
+    }
+    return ingest_fasta_batch(g, ptrs, n_bytes, n_files, flags, h_header_table, cap_headers, infos);
     PDG_API_END
 }
 
@@ -190,6 +215,11 @@ int pdg_get_build_stats(pdg_graph *g, pdg_build_stats *out) {
     PDG_API_BEGIN
     *out = g->stats;
     out->kernel_launches = g->launches;
+    out->ms_ingest_a = g->ms_ingest[0];
+    out->ms_ingest_b = g->ms_ingest[1];
+    out->ms_ingest_c = g->ms_ingest[2];
+    out->ingest_bytes = g->ingest_bytes;
+    out->ingest_launches = g->ingest_launches;
     return PDG_OK;
     PDG_API_END
 }

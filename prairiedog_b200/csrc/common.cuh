@@ -153,13 +153,23 @@ struct pdg_graph {
     const uint64_t *u_codes = nullptr;   // points at g_codes, x_codes or u_codes_buf
 
     // ---- scratch ----
+    pdg::DevBuf m3_tile_info;
     pdg::DevBuf recA, recB, scratch0, scratch1, scratch2, status, hist;
     pdg::DevBuf q_a, q_b, q_cnt, q_cnt_g, q_off, q_hits, small;
     uint64_t q_n = 0, q_total = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<cudaEvent_t> k_events;   // per-kernel timing of msd3.cu / ingest_batch.cu
     bool collect_sort_stats = false;   // radix.cu times its pass kernels into stats
 
     pdg_build_stats stats{};
+
+    // ---- batched ingest (ingest_batch.cu) ----
+    pdg::DevBuf stage, fb_files, fb_summ, fb_prefix, fb_totals;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t fb_ev_ready = nullptr;
+    std::vector<cudaEvent_t> fb_events, i_events;
+    float ms_ingest[3] = {0, 0, 0};
+    uint64_t ingest_bytes = 0, ingest_launches = 0;
 
     // ---- multi GPU ----
     void *nccl_comm = nullptr;
@@ -188,6 +198,10 @@ uint64_t *radix_sort_keys(pdg_graph *g, uint64_t *a, uint64_t *b, uint64_t n, in
 // ---- ingest.cu ----
 int ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes, uint64_t *h_header_table,
                  uint64_t cap_headers, pdg_ingest_info *info);
+
+// ---- ingest_batch.cu ----
+int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t *n_bytes, uint32_t n_files,
+                       int flags, uint64_t *h_table, uint64_t cap_headers, pdg_ingest_info *infos);
 
 // ---- build.cu ----
 int finalize(pdg_graph *g, int flags);

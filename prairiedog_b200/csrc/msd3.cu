@@ -22,38 +22,36 @@ namespace pdg {
 struct M3Plan {
     int b1, b2, b3;              // digit widths, low to high
     uint32_t n_tiles, ch, n_chunks;
-    uint64_t pos0, pos1;
+    uint64_t base0;              // first position of tile 0 (a multiple of 32)
 };
 
-struct M3Contigs {
-    uint64_t ci;
-    bool simple;   // every window of the tile is a k-mer of one contig
-};
-
-__device__ __forceinline__ void m3_tile_contigs(const ContigTable &ct, uint64_t p0, uint64_t p1, int k, M3Contigs *tc) {
+// ---- per-tile contig lookup ----------------------------------------------------------------------
+// tile_info[tile] = index of the last contig that begins at or before the tile (0 if none), with
+// M3_SIMPLE set when every window of the tile is a k-mer of that contig.
+__global__ void m3_tile_info_kernel(ContigTable ct, M3Plan pl, int k, uint32_t *__restrict__ tile_info) {
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile >= pl.n_tiles) return;
+    const uint64_t p0 = pl.base0 + (uint64_t)tile * M3_TILE;
     const uint64_t ci = contig_of(ct, p0);
-    tc->ci = ci;
-    tc->simple = p0 >= ct.begin[ci] && p1 + k <= ct.end[ci] + 1;
-}
-__device__ __forceinline__ bool m3_valid(const ContigTable &ct, const M3Contigs &tc, uint64_t p, int k) {
-    if (tc.simple) return true;
-    uint64_t ci = tc.ci;
-    while (ci + 1 < ct.n && ct.begin[ci + 1] <= p) ++ci;
-    return p >= ct.begin[ci] && p + k <= ct.end[ci];
+    const bool simple = p0 >= ct.begin[ci] && p0 + M3_TILE - 1 + k <= ct.end[ci];
+    tile_info[tile] = (uint32_t)ci | (simple ? M3_SIMPLE : 0u);
 }
 
 // ---- histograms from the packed genome --------------------------------------------------------
 // H1T[d3][tile]; H12[chunk][d3 << b2 | d2]; tot32[cell] += chunk counts.
-// One CTA per chunk; every WARP takes whole tiles on its own (private d3 counters, its own copy of
-// the tile's packed words), so there is no block barrier inside the tile loop.
+// One CTA per chunk; every WARP takes whole tiles on its own (private d3 counters and validity
+// words), so there is no block barrier inside the tile loop.  Round i of a tile: lane l looks at
+// position 32*i + l, i.e. all lanes share the packed words i and i+1.
 static constexpr int M3H_THREADS = 1024;
 static constexpr int M3H_WARPS = M3H_THREADS / 32;
-__global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const unsigned long long *__restrict__ packed,
-                                                              uint64_t packed_words, int k, ContigTable ct, M3Plan pl,
+__global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const uint2 *__restrict__ packed, uint64_t packed_words,
+                                                              int k, ContigTable ct, M3Plan pl,
+                                                              const uint32_t *__restrict__ tile_info,
                                                               uint32_t *__restrict__ H1T, uint32_t *__restrict__ H12,
                                                               unsigned int *__restrict__ tot32) {
     extern __shared__ uint32_t h12[];   // [cells]
     __shared__ uint32_t h1[M3H_WARPS][128];
+    __shared__ uint32_t vms[M3H_WARPS][M3_TILE_WORDS];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t cells = 1u << (pl.b3 + pl.b2), B3 = 1u << pl.b3;
     const int sh2 = pl.b1, sh3 = pl.b1 + pl.b2;
@@ -61,28 +59,34 @@ __global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const unsigned lon
     __syncthreads();
     const uint32_t t0 = blockIdx.x * pl.ch, t1 = min(t0 + pl.ch, pl.n_tiles);
     for (uint32_t tile = t0 + w; tile < t1; tile += M3H_WARPS) {
-        const uint64_t p0 = pl.pos0 + (uint64_t)tile * M3_TILE, p1 = min(p0 + (uint64_t)M3_TILE, pl.pos1);
+        const uint64_t w0 = (pl.base0 >> 5) + (uint64_t)tile * M3_TILE_WORDS;
+        const uint32_t info = tile_info[tile];
         for (int i = lane; i < 128; i += 32) h1[w][i] = 0;
-        M3Contigs tc;
-        m3_tile_contigs(ct, p0, p1, k, &tc);
+        const bool simple = (info & M3_SIMPLE) != 0;
+        if (!simple)
+            for (int i = lane; i < M3_TILE_WORDS; i += 32) vms[w][i] = m3_valid_word(ct, w0 + i, info & ~M3_SIMPLE, k);
         __syncwarp();
-        // lane l walks positions p0 + 32*i + l: the window starts in word (p >> 5) and may spill
-        // into the next one, so keep a sliding pair of words
-        const uint64_t w0 = p0 >> 5;
-        const uint32_t lead = (uint32_t)(p0 & 31u);
-        const uint32_t n_steps = (uint32_t)((p1 - p0 + 31) >> 5);
-        for (uint32_t i = 0; i < n_steps; ++i) {
-            const uint64_t q = (uint64_t)lead + 32u * i + lane;       // slot relative to word w0
-            const uint64_t p = p0 + 32u * i + lane;
-            const uint64_t wi = w0 + (q >> 5);
-            const unsigned long long hi = wi < packed_words ? packed[wi] : 0ULL;
-            const unsigned long long lo = wi + 1 < packed_words ? packed[wi + 1] : 0ULL;
-            const uint32_t sft = 2u * (uint32_t)(q & 31u);
-            const unsigned long long x = sft ? ((hi << sft) | (lo >> (64 - sft))) : hi;
-            const uint32_t code = (uint32_t)(x >> (64 - 2 * k));
-            if (p < p1 && m3_valid(ct, tc, p, k)) {
-                atomicAdd(&h1[w][code >> sh3], 1u);
-                atomicAdd(&h12[code >> sh2], 1u);
+        // lane l keeps packed words w0 + 32*g + l for the current group g of 32 rounds
+        for (int g = 0; g < M3_TILE_WORDS / 32; ++g) {
+            const uint64_t wa = w0 + 32 * g + lane;
+            const uint2 mine = wa < packed_words ? packed[wa] : make_uint2(0u, 0u);
+            const uint64_t wb = w0 + 32 * g + 32;
+            const uint2 next = (lane == 0 && wb < packed_words) ? packed[wb] : make_uint2(0u, 0u);
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) {
+                uint2 hi, lo;
+                hi.x = __shfl_sync(0xffffffffu, mine.x, i);
+                hi.y = __shfl_sync(0xffffffffu, mine.y, i);
+                // only the top half of the following word is ever needed (k <= 11)
+                const uint32_t nx = __shfl_sync(0xffffffffu, i == 31 ? next.y : mine.y, (i + 1) & 31);
+                lo.x = 0u;
+                lo.y = nx;
+                const uint32_t code = m3_code_at(hi, lo, lane, k);
+                const bool ok = simple || ((vms[w][32 * g + i] >> lane) & 1u);
+                if (ok) {
+                    atomicAdd(&h1[w][code >> sh3], 1u);
+                    atomicAdd(&h12[code >> sh2], 1u);
+                }
             }
         }
         __syncwarp();
@@ -147,41 +151,40 @@ __global__ void __launch_bounds__(256) m3_scan_chunks_kernel(uint32_t *__restric
 }
 
 // ---- pass 1: position tile -> records grouped by d3 ---------------------------------------------
-__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass1_kernel(const unsigned long long *__restrict__ packed,
+__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass1_kernel(const uint2 *__restrict__ packed,
                                                                  uint64_t packed_words, int k, ContigTable ct, M3Plan pl,
+                                                                 const uint32_t *__restrict__ tile_info,
                                                                  const uint32_t *__restrict__ O1T,
                                                                  uint64_t *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char m3_raw[];
     M3Smem &sm = *reinterpret_cast<M3Smem *>(m3_raw);
-    __shared__ unsigned long long words[M3_WORDS];
-    __shared__ M3Contigs tc;
+    __shared__ uint2 words[M3_TILE_WORDS + 2];
+    __shared__ uint32_t vm[M3_TILE_WORDS];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t tile = blockIdx.x, B3 = 1u << pl.b3;
     const int sh3 = pl.b1 + pl.b2;
-    const uint64_t p0 = pl.pos0 + (uint64_t)tile * M3_TILE, p1 = min(p0 + (uint64_t)M3_TILE, pl.pos1);
-    for (int i = tid; i < M3_WORDS; i += M3_THREADS) {
-        const uint64_t wi = (p0 >> 5) + i;
-        words[i] = wi < packed_words ? packed[wi] : 0ULL;
-    }
+    const uint64_t w0 = (pl.base0 >> 5) + (uint64_t)tile * M3_TILE_WORDS;
+    const uint32_t info = tile_info[tile];
+    if (tid < M3_TILE_WORDS + 2) words[tid] = w0 + tid < packed_words ? packed[w0 + tid] : make_uint2(0u, 0u);
+    if (tid < M3_TILE_WORDS)
+        vm[tid] = (info & M3_SIMPLE) ? 0xffffffffu : m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, k);
     if (tid < (int)B3) sm.cursor[tid] = O1T[(size_t)tid * pl.n_tiles + tile];
-    if (tid == 0) m3_tile_contigs(ct, p0, p1, k, &tc);
+    m3_clear_table(sm);
     __syncthreads();
-    const uint32_t lead = (uint32_t)(p0 & 31u);
-    uint64_t r[M3_ITEMS];
-    uint32_t dg[M3_ITEMS];
+    const uint32_t pbase = (uint32_t)(w0 << 5) + w * M3_WARP_TILE + lane;
+    uint32_t pos[M3_ITEMS], code[M3_ITEMS], dg[M3_ITEMS];
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
-        const uint32_t li = w * (M3_ITEMS * 32) + j * 32 + lane;
-        const uint64_t p = p0 + li;
-        const uint32_t code = (uint32_t)kmer_at(words, lead + li, k);
-        r[j] = ((uint64_t)code << 32) | (uint32_t)p;
-        dg[j] = (p < p1 && m3_valid(ct, tc, p, k)) ? (code >> sh3) : M3_DROP;
+        const int wi = w * M3_ITEMS + j;
+        pos[j] = pbase + 32 * j;
+        code[j] = m3_code_at(words[wi], words[wi + 1], lane, k);
+        dg[j] = ((vm[wi] >> lane) & 1u) ? (code[j] >> sh3) : B3;
     }
-    m3_partition_tile<false>(sm, r, dg, sh3, (int)B3, out, nullptr);
+    m3_partition_tile<false>(sm, pos, code, dg, (int)B3, [sh3](uint32_t c) { return c >> sh3; }, out, nullptr);
 }
 
 // ---- pass 2: range (chunk, d3) -> grouped by (d3, d2) --------------------------------------------
-__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass2_kernel(const uint64_t *__restrict__ in, M3Plan pl,
+__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass2_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ O1T,
                                                                  const uint32_t *__restrict__ O2,
                                                                  const uint32_t *__restrict__ base32,
@@ -196,71 +199,77 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass2_kernel(const uint64_t 
                                                 : base32[(size_t)(d3 + 1) << pl.b2];
     if (begin >= end) return;
     if (tid < (int)B2) sm.cursor[tid] = O2[(size_t)c * (B3 * B2) + ((size_t)d3 << pl.b2) + tid];
+    m3_clear_table(sm);
     __syncthreads();
+    const int b1 = pl.b1;
+    const uint32_t m2 = B2 - 1;
     for (uint32_t t0 = begin; t0 < end; t0 += M3_TILE) {
         const uint32_t tile_n = min((uint32_t)M3_TILE, end - t0);
-        uint64_t r[M3_ITEMS];
-        uint32_t dg[M3_ITEMS];
+        const uint2 *src = in + t0 + w * M3_WARP_TILE + lane;
+        const uint32_t li0 = w * M3_WARP_TILE + lane;
+        uint32_t pos[M3_ITEMS], code[M3_ITEMS], dg[M3_ITEMS];
 #pragma unroll
         for (int j = 0; j < M3_ITEMS; ++j) {
-            const uint32_t li = w * (M3_ITEMS * 32) + j * 32 + lane;
-            const bool ok = li < tile_n;
-            r[j] = ok ? in[t0 + li] : 0ULL;
-            dg[j] = ok ? (((uint32_t)(r[j] >> 32) >> pl.b1) & (B2 - 1)) : M3_DROP;
+            const bool ok = li0 + 32 * j < tile_n;
+            const uint2 r = ok ? src[32 * j] : make_uint2(0u, 0u);
+            pos[j] = r.x;
+            code[j] = r.y;
+            dg[j] = ok ? ((r.y >> b1) & m2) : B2;
         }
-        m3_partition_tile<false>(sm, r, dg, pl.b1, (int)B2, out, nullptr);
+        m3_partition_tile<false>(sm, pos, code, dg, (int)B2, [b1, m2](uint32_t cd) { return (cd >> b1) & m2; }, out,
+                                 nullptr);
     }
 }
 
 // ---- pass 3: bucket (d3, d2): count d1, row starts, position column ------------------------------
-__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass3_kernel(const uint64_t *__restrict__ in, M3Plan pl,
+__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass3_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ base32,
                                                                  uint32_t *__restrict__ rowtab,
                                                                  uint32_t *__restrict__ out_pos) {
     extern __shared__ __align__(16) unsigned char m3_raw[];
     M3Smem &sm = *reinterpret_cast<M3Smem *>(m3_raw);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const uint32_t B1 = 1u << pl.b1, cell = blockIdx.x;
+    const uint32_t B1 = 1u << pl.b1, m1 = B1 - 1, cell = blockIdx.x;
     const uint32_t begin = base32[cell], end = base32[cell + 1];
-    // count d1 over the bucket (sm.bstart doubles as the histogram)
-    if (tid < M3_MAX_BINS) sm.bstart[tid] = 0;
+    // count d1 over the bucket (sm.delta doubles as the histogram)
+    sm.delta[tid] = 0;
+    m3_clear_table(sm);
     __syncthreads();
-    for (uint32_t i = begin + tid; i < end; i += M3_THREADS)
-        atomicAdd(&sm.bstart[(uint32_t)(in[i] >> 32) & (B1 - 1)], 1u);
+    for (uint32_t i = begin + tid; i < end; i += M3_THREADS) atomicAdd(&sm.delta[in[i].y & m1], 1u);
     __syncthreads();
-    if (w == 0) {
-        constexpr int PER = M3_MAX_BINS / 32;
-        uint32_t v[PER], s = 0;
-#pragma unroll
-        for (int i = 0; i < PER; ++i) { v[i] = sm.bstart[lane * PER + i]; s += v[i]; }
-        uint32_t inc = s;
+    {   // exclusive scan of the 256 counts -> first occurrence of every code of the bucket
+        const uint32_t v = sm.delta[tid];
+        uint32_t inc = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
             if (lane >= o) inc += t;
         }
-        uint32_t ex = begin + inc - s;
+        if (lane == 31) sm.wsum[w] = inc;
+        __syncthreads();
+        uint32_t base = begin;
 #pragma unroll
-        for (int i = 0; i < PER; ++i) {
-            const uint32_t b = lane * PER + i;
-            sm.cursor[b] = ex;
-            if (b < B1) rowtab[((size_t)cell << pl.b1) + b] = ex;   // first occurrence of code (cell, b)
-            ex += v[i];
-        }
+        for (int ww = 0; ww < M3_WARPS; ++ww)
+            if (ww < w) base += sm.wsum[ww];
+        const uint32_t ex = base + inc - v;
+        sm.cursor[tid] = ex;
+        if (tid < (int)B1) rowtab[((size_t)cell << pl.b1) + tid] = ex;
     }
     __syncthreads();
     for (uint32_t t0 = begin; t0 < end; t0 += M3_TILE) {
         const uint32_t tile_n = min((uint32_t)M3_TILE, end - t0);
-        uint64_t r[M3_ITEMS];
-        uint32_t dg[M3_ITEMS];
+        const uint2 *src = in + t0 + w * M3_WARP_TILE + lane;
+        const uint32_t li0 = w * M3_WARP_TILE + lane;
+        uint32_t pos[M3_ITEMS], code[M3_ITEMS], dg[M3_ITEMS];
 #pragma unroll
         for (int j = 0; j < M3_ITEMS; ++j) {
-            const uint32_t li = w * (M3_ITEMS * 32) + j * 32 + lane;
-            const bool ok = li < tile_n;
-            r[j] = ok ? in[t0 + li] : 0ULL;
-            dg[j] = ok ? ((uint32_t)(r[j] >> 32) & (B1 - 1)) : M3_DROP;
+            const bool ok = li0 + 32 * j < tile_n;
+            const uint2 r = ok ? src[32 * j] : make_uint2(0u, 0u);
+            pos[j] = r.x;
+            code[j] = r.y;
+            dg[j] = ok ? (r.y & m1) : B1;
         }
-        m3_partition_tile<true>(sm, r, dg, 0, (int)B1, nullptr, out_pos);
+        m3_partition_tile<true>(sm, pos, code, dg, (int)B1, [m1](uint32_t cd) { return cd & m1; }, nullptr, out_pos);
     }
 }
 
@@ -283,14 +292,13 @@ __global__ void m3_compact_rows_kernel(const uint32_t *__restrict__ rowtab, cons
 void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     cudaStream_t s = g->stream;
     const int k = g->k;
-    const uint64_t n = hc.n_kmers, span = hc.pos1 - hc.pos0;
+    const uint64_t n = hc.n_kmers;
     M3Plan pl{};
     pl.b1 = std::min(8, 2 * k);
     pl.b2 = std::min(7, 2 * k - pl.b1);
     pl.b3 = 2 * k - pl.b1 - pl.b2;
-    pl.pos0 = hc.pos0;
-    pl.pos1 = hc.pos1;
-    pl.n_tiles = (uint32_t)((span + M3_TILE - 1) / M3_TILE);
+    pl.base0 = hc.pos0 & ~31ULL;
+    pl.n_tiles = (uint32_t)((hc.pos1 - pl.base0 + M3_TILE - 1) / M3_TILE);
     const uint32_t B3 = 1u << pl.b3, cells = 1u << (pl.b3 + pl.b2);
     pl.ch = std::max<uint32_t>(1, (3500u * B3) / M3_TILE);   // ranges of pass 2 average ~3500 records
     pl.n_chunks = (pl.n_tiles + pl.ch - 1) / pl.ch;
@@ -303,6 +311,8 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     g->recA.reserve(std::max<size_t>(n * 8, n_codes * 4), s);
     g->recB.reserve(n * 8, s);
     g->g_pos.reserve(n * 4, s);
+    g->m3_tile_info.reserve((size_t)pl.n_tiles * 4, s);
+    uint32_t *tile_info = g->m3_tile_info.as<uint32_t>();
     uint32_t *H1T = g->status.as<uint32_t>(), *H12 = g->scratch1.as<uint32_t>();
     unsigned int *tot32 = g->hist.as<unsigned int>();
     uint32_t *base32 = g->hist.as<uint32_t>() + cells;
@@ -317,37 +327,52 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
         PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
         attr_set = true;
     }
-    const unsigned long long *packed = g->packed.as<unsigned long long>();
+    const uint2 *packed = g->packed.as<uint2>();
     const uint64_t pw = g->packed.cap / 8;
-    m3_hist_kernel<<<pl.n_chunks, M3H_THREADS, cells * 4, s>>>(packed, pw, k, ct, pl, H1T, H12, tot32);
+    m3_tile_info_kernel<<<(pl.n_tiles + 255) / 256, 256, 0, s>>>(ct, pl, k, tile_info);
     PDG_LAUNCHED(g);
+    // CUDA events around every launch of the sort (bench.py's roofline numbers): event i precedes
+    // stage i of {hist, scans, pass 1, pass 2, pass 3}
+    const bool timed = g->collect_sort_stats;
+    if (timed)
+        while (g->k_events.size() < 6) {
+            cudaEvent_t ev;
+            PDG_CUDA(cudaEventCreate(&ev));
+            g->k_events.push_back(ev);
+        }
+    auto mark = [&](int i) { if (timed) PDG_CUDA(cudaEventRecord(g->k_events[i], s)); };
+    mark(0);
+    m3_hist_kernel<<<pl.n_chunks, M3H_THREADS, cells * 4, s>>>(packed, pw, k, ct, pl, tile_info, H1T, H12, tot32);
+    PDG_LAUNCHED(g);
+    mark(1);
     m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32);
     PDG_LAUNCHED(g);
     m3_scan_tiles_kernel<<<B3, 1024, 0, s>>>(H1T, pl.n_tiles, base32, pl.b2);
     PDG_LAUNCHED(g);
     m3_scan_chunks_kernel<<<(cells + 255) / 256, 256, 0, s>>>(H12, pl.n_chunks, cells, base32);
     PDG_LAUNCHED(g);
-
-    const bool timed = g->collect_sort_stats;
-    if (timed && !g->ev0) {
-        PDG_CUDA(cudaEventCreate(&g->ev0));
-        PDG_CUDA(cudaEventCreate(&g->ev1));
-    }
-    if (timed) PDG_CUDA(cudaEventRecord(g->ev0, s));
-    m3_pass1_kernel<<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, ct, pl, H1T, g->recA.as<uint64_t>());
+    mark(2);
+    m3_pass1_kernel<<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, ct, pl, tile_info, H1T, g->recA.as<uint64_t>());
     PDG_LAUNCHED(g);
-    m3_pass2_kernel<<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem), s>>>(g->recA.as<uint64_t>(), pl, H1T, H12, base32,
+    mark(3);
+    m3_pass2_kernel<<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem), s>>>(g->recA.as<uint2>(), pl, H1T, H12, base32,
                                                                          g->recB.as<uint64_t>());
     PDG_LAUNCHED(g);
-    m3_pass3_kernel<<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint64_t>(), pl, base32, rowtab,
+    mark(4);
+    m3_pass3_kernel<<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, base32, rowtab,
                                                               g->g_pos.as<uint32_t>());
     PDG_LAUNCHED(g);
+    mark(5);
     if (timed) {
-        PDG_CUDA(cudaEventRecord(g->ev1, s));
-        PDG_CUDA(cudaEventSynchronize(g->ev1));
-        float ms = 0;
-        cudaEventElapsedTime(&ms, g->ev0, g->ev1);
-        g->stats.ms_sort_kernel_avg = ms / 3.0f;
+        PDG_CUDA(cudaEventSynchronize(g->k_events[5]));
+        float ms[5] = {0, 0, 0, 0, 0};
+        for (int i = 0; i < 5; ++i) cudaEventElapsedTime(&ms[i], g->k_events[i], g->k_events[i + 1]);
+        g->stats.ms_hist = ms[0];
+        g->stats.ms_scans = ms[1];
+        g->stats.ms_pass[0] = ms[2];
+        g->stats.ms_pass[1] = ms[3];
+        g->stats.ms_pass[2] = ms[4];
+        g->stats.ms_sort_kernel_avg = (ms[2] + ms[3] + ms[4]) / 3.0f;
         g->stats.sort_kernel_launches = 3;
     }
     g->stats.sort_passes = 3;

@@ -8,110 +8,133 @@ static constexpr int M3_THREADS = 256;
 static constexpr int M3_WARPS = M3_THREADS / 32;
 static constexpr int M3_ITEMS = 16;
 static constexpr int M3_TILE = M3_THREADS * M3_ITEMS;   // 4096 items per tile
+static constexpr int M3_WARP_TILE = 32 * M3_ITEMS;      // 512 consecutive items per warp
 static constexpr int M3_MAX_BINS = 256;
-static constexpr int M3_WORDS = M3_TILE / 32 + 2;       // packed words staged per position tile
+static constexpr int M3_TAB = M3_MAX_BINS + 1;          // + the trash bin of items that are not records
+static constexpr int M3_TILE_WORDS = M3_TILE / 32;      // packed words per position tile
 static constexpr int kMsd3MaxBits = 22;                 // k <= 11: digits (<=7, <=7, <=8)
-static constexpr uint32_t M3_DROP = 0xFFFFFFFFu;        // digit of an item that is not a record
+static constexpr uint32_t M3_SIMPLE = 0x80000000u;      // tile_info flag: every window is a k-mer
 
 // dynamic shared memory of one tile partition
 struct M3Smem {
-    uint64_t stage[M3_TILE];                 // the tile in sorted order
-    uint2 wtab[M3_WARPS][M3_MAX_BINS];       // per (warp, bin): {lane mask of the round, count}
-    uint32_t bstart[M3_MAX_BINS];            // start of the bin inside the tile
-    uint32_t delta[M3_MAX_BINS];             // global offset of the bin's run minus bstart
+    uint2 stage[M3_TILE];                    // the tile in sorted order: {position, code}
+    uint2 wtab[M3_WARPS][M3_TAB];            // per (warp, bin): {lane mask of the round, count / base}
+    uint32_t delta[M3_MAX_BINS];             // global offset of the bin's run minus its start in stage
     uint32_t cursor[M3_MAX_BINS];            // global offset where this CTA writes the bin next
-    uint32_t total;                          // records in the current tile
+    uint32_t wsum[M3_WARPS];
+    uint32_t total;                          // records of the current tile
 };
 
 #ifdef __CUDACC__
-// Stable partition of one tile by a digit.  r / dg: the items of this thread in warp-striped order
-// (item j of lane l of warp w is tile element w*512 + j*32 + l); dg == M3_DROP drops the item.
-// On entry sm.cursor[b] is the global offset of the first record of bin b of this tile; on exit
-// it has advanced by the tile's count (so a CTA can walk consecutive tiles of one range).
-// OUT4: write the low 32 bits (position) to out4, else the record to out8.
+// k-mer code of position (32 * word + lane): hi / lo are the packed words `word` and `word + 1`
+// (big endian, 32 residues each).  Works on 32-bit halves: one funnel shift per window.
+__device__ __forceinline__ uint32_t m3_code_at(uint2 hi, uint2 lo, int lane, int k) {
+    const uint32_t x = lane < 16 ? hi.y : hi.x, y = lane < 16 ? hi.x : lo.y;
+    return __funnelshift_l(y, x, 2 * (lane & 15)) >> (32 - 2 * k);
+}
+
+// Validity bits of the 32 windows starting in packed word `word` (positions 32*word ..): bit l is
+// set iff some contig holds the whole window.  ci: any contig index with begin[ci] <= 32*word, or 0.
+__device__ __forceinline__ uint32_t m3_valid_word(const ContigTable &ct, uint64_t word, uint64_t ci, int k) {
+    const uint64_t p0 = word << 5, p1 = p0 + 32;
+    uint32_t m = 0;
+    while (ci + 1 < ct.n && ct.begin[ci + 1] <= p0) ++ci;
+    for (; ci < ct.n; ++ci) {
+        const uint64_t b = ct.begin[ci];
+        if (b >= p1) break;
+        const uint64_t e = ct.end[ci];
+        if (e < p0 + k) continue;
+        const uint64_t lo = b > p0 ? b - p0 : 0, hi = e - k - p0;   // valid starts [lo, hi] relative to p0
+        if (lo > 31) continue;
+        const uint32_t upto = hi >= 31 ? 0xffffffffu : ((2u << (uint32_t)hi) - 1u);
+        m |= upto & ~((1u << (uint32_t)lo) - 1u);
+    }
+    return m;
+}
+
+// Stable partition of one tile by a digit.  Item j of lane l of warp w is tile element
+// w*512 + j*32 + l; dg[j] in [0, BINS) or BINS (= not a record, dropped; dg is clobbered).
+// pos[j] / code[j] is the record.  On entry sm.cursor[b] is the global offset of the first record of bin b of this
+// tile; on exit it has advanced by the tile's count (a CTA can walk consecutive tiles of a range).
+// OUT4: write the position to out4, else (code << 32 | position) to out8.
 // Ranking: every lane ORs its bit into the mask of its (warp, bin) entry, reads {mask, count}
-// back and the lowest lane of each group folds the mask into the count -- no warp match (MATCH.ANY
-// sustains only ~0.5 lanes/cycle/SM on sm_100, shared-memory atomics ~10).
-template <bool OUT4>
-__device__ __forceinline__ void m3_partition_tile(M3Smem &sm, uint64_t (&r)[M3_ITEMS], uint32_t (&dg)[M3_ITEMS],
-                                                  int shift, int BINS, uint64_t *__restrict__ out8,
+// back, and the lowest lane of each group folds the mask into the count -- no warp match
+// (MATCH.ANY sustains ~0.5 lanes/cycle/SM on sm_100, shared-memory atomics ~10).
+// Needs: wtab zeroed and a barrier since; leaves wtab zeroed and ends with a barrier.
+template <bool OUT4, typename DigitFn>
+__device__ __forceinline__ void m3_partition_tile(M3Smem &sm, const uint32_t (&pos)[M3_ITEMS],
+                                                  const uint32_t (&code)[M3_ITEMS], uint32_t (&dg)[M3_ITEMS],
+                                                  const int BINS, DigitFn digit, uint64_t *__restrict__ out8,
                                                   uint32_t *__restrict__ out4) {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const uint32_t lt = (1u << lane) - 1u;
-    for (int i = tid; i < M3_WARPS * M3_MAX_BINS; i += M3_THREADS) (&sm.wtab[0][0])[i] = make_uint2(0u, 0u);
-    __syncthreads();
-    uint32_t rank[M3_ITEMS];
+    const uint32_t lt = (1u << lane) - 1u, bit = 1u << lane;
     uint2 *wt = sm.wtab[w];
+    // dg[j] becomes digit | rank-within-(warp, bin) << 16 (one register per item instead of two)
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
-        const bool ok = dg[j] != M3_DROP;
-        if (ok) atomicOr(&wt[dg[j]].x, 1u << lane);
+        uint2 *e = wt + dg[j];
+        atomicOr(&e->x, bit);
         __syncwarp();
-        uint2 mc = make_uint2(0u, 0u);
-        if (ok) mc = wt[dg[j]];
-        rank[j] = mc.y + __popc(mc.x & lt);
+        const uint2 mc = *e;
+        const uint32_t below = mc.x & lt;
+        dg[j] |= (mc.y + __popc(below)) << 16;
         __syncwarp();
-        if (ok && (mc.x & lt) == 0) wt[dg[j]] = make_uint2(0u, mc.y + __popc(mc.x));
+        if (below == 0) *e = make_uint2(0u, mc.y + __popc(mc.x));
         __syncwarp();
     }
     __syncthreads();
-    // per bin: exclusive offsets of the warps, tile count
-    for (int b = tid; b < BINS; b += M3_THREADS) {
-        uint32_t run = 0;
+    // bin `tid`: counts of the warps -> exclusive bases, tile count
+    uint32_t c[M3_WARPS], tot = 0;
+    if (tid < BINS) {
 #pragma unroll
-        for (int ww = 0; ww < M3_WARPS; ++ww) {
-            const uint32_t c = sm.wtab[ww][b].y;
-            sm.wtab[ww][b].y = run;
-            run += c;
-        }
-        sm.bstart[b] = run;
+        for (int ww = 0; ww < M3_WARPS; ++ww) { c[ww] = sm.wtab[ww][tid].y; tot += c[ww]; }
     }
+    uint32_t inc = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) sm.wsum[w] = inc;
     __syncthreads();
-    if (w == 0) {   // exclusive scan of the bin counts by one warp
-        constexpr int PER = M3_MAX_BINS / 32;
-        uint32_t v[PER], s = 0;
+    uint32_t base = 0, all = 0;
 #pragma unroll
-        for (int i = 0; i < PER; ++i) {
-            const int b = lane * PER + i;
-            v[i] = b < BINS ? sm.bstart[b] : 0u;
-            s += v[i];
-        }
-        uint32_t inc = s;
+    for (int ww = 0; ww < M3_WARPS; ++ww) {
+        const uint32_t v = sm.wsum[ww];
+        if (ww < w) base += v;
+        all += v;
+    }
+    if (tid < BINS) {
+        uint32_t run = base + inc - tot;           // start of the bin inside the tile
+        const uint32_t cur = sm.cursor[tid];
+        sm.delta[tid] = cur - run;
+        sm.cursor[tid] = cur + tot;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        uint32_t ex = inc - s;
-#pragma unroll
-        for (int i = 0; i < PER; ++i) {
-            const int b = lane * PER + i;
-            if (b < BINS) {
-                sm.bstart[b] = ex;
-                const uint32_t cur = sm.cursor[b];
-                sm.delta[b] = cur - ex;
-                sm.cursor[b] = cur + v[i];
-                ex += v[i];
-            }
-        }
-        if (lane == 31) sm.total = ex;
+        for (int ww = 0; ww < M3_WARPS; ++ww) { sm.wtab[ww][tid].y = run; run += c[ww]; }
     }
     __syncthreads();
 #pragma unroll
-    for (int j = 0; j < M3_ITEMS; ++j)
-        if (dg[j] != M3_DROP) sm.stage[sm.bstart[dg[j]] + wt[dg[j]].y + rank[j]] = r[j];
+    for (int j = 0; j < M3_ITEMS; ++j) {
+        const uint32_t d = dg[j] & 0xffffu;
+        if (d != (uint32_t)BINS) sm.stage[wt[d].y + (dg[j] >> 16)] = make_uint2(pos[j], code[j]);
+    }
     __syncthreads();
-    const uint32_t total = sm.total, mask = BINS - 1;
+    // re-arm the table for the next tile while the stage drains
+    for (int i = tid; i < M3_WARPS * M3_TAB; i += M3_THREADS) (&sm.wtab[0][0])[i] = make_uint2(0u, 0u);
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const uint32_t s = j * M3_THREADS + tid;
-        if (s < total) {
-            const uint64_t x = sm.stage[s];
-            const uint32_t d = ((uint32_t)(x >> 32) >> shift) & mask;
-            if (OUT4) out4[sm.delta[d] + s] = (uint32_t)x; else out8[sm.delta[d] + s] = x;
+        if (s < all) {
+            const uint2 x = sm.stage[s];
+            const uint32_t at = sm.delta[digit(x.y)] + s;
+            if (OUT4) out4[at] = x.x; else out8[at] = ((uint64_t)x.y << 32) | x.x;
         }
     }
     __syncthreads();
+}
+
+__device__ __forceinline__ void m3_clear_table(M3Smem &sm) {
+    for (int i = threadIdx.x; i < M3_WARPS * M3_TAB; i += M3_THREADS) (&sm.wtab[0][0])[i] = make_uint2(0u, 0u);
 }
 #endif
 

@@ -64,6 +64,30 @@ class Engine(object):
             check(rc)
             return info, table[:int(info.n_headers)]
 
+    def ingest_batch(self, ptrs, sizes, host=False):
+        """pdg_ingest_fasta_batch.  ptrs: raw pointers (device, or host when ``host``) of the file
+        images, sizes: their byte counts.  Returns (infos, table[n_rows, 4], row_base[n_files+1]):
+        infos is a numpy structured array with the fields of pdg_ingest_info, file f owns rows
+        table[row_base[f]:row_base[f+1]] = {byte_begin, byte_end, residue_index, hash}."""
+        n = len(ptrs)
+        p = (ctypes.c_void_p * max(n, 1))(*[int(x) if x else None for x in ptrs])
+        sz = np.ascontiguousarray(sizes, dtype=np.uint64)
+        infos = np.zeros(n, dtype=_ffi.INGEST_INFO_DTYPE)
+        cap = max(256 * n, 1024) if getattr(self, "_batch_rows", 0) == 0 else self._batch_rows
+        while True:
+            table = np.empty((cap, 4), dtype=np.uint64)
+            rc = self.lib.pdg_ingest_fasta_batch(self.h, p, sz.ctypes.data, n, _ffi.PDG_IN_HOST if host else 0,
+                                                 table.ctypes.data, cap, infos.ctypes.data)
+            if rc == _ffi.PDG_E_CAPACITY:
+                cap = int(infos["n_headers"].sum())
+                continue
+            check(rc)
+            break
+        row_base = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum(infos["n_headers"].astype(np.int64), out=row_base[1:])
+        self._batch_rows = max(int(row_base[-1]), 1)
+        return infos, table[:int(row_base[-1])], row_base
+
     def add_contigs(self, begin, length, type_id):
         begin, length = _u64(begin), _u64(length)
         type_id = np.ascontiguousarray(type_id, dtype=np.uint32)
@@ -116,7 +140,9 @@ class Engine(object):
     def stats(self):
         st = _ffi.BuildStats()
         check(self.lib.pdg_get_build_stats(self.h, ctypes.byref(st)))
-        return {f: getattr(st, f) for f, _ in st._fields_ if f != "pad"}
+        out = {f: getattr(st, f) for f, _ in st._fields_ if not f.startswith("pad")}
+        out["ms_pass"] = list(out["ms_pass"])
+        return out
 
     def export_nodes(self):
         n = self.counts()[0]

@@ -24,7 +24,7 @@ def test_library_exports_header_symbols(lib_built):
         assert hasattr(lib, n), n
     assert sorted(_ffi.SIGNATURES) == names
     lib.pdg_abi_version.restype = ctypes.c_int
-    assert lib.pdg_abi_version() == 2
+    assert lib.pdg_abi_version() == 3
 
 
 def test_struct_layouts(lib_built):
@@ -32,7 +32,14 @@ def test_struct_layouts(lib_built):
     from prairiedog_b200.engine import HIT_DTYPE
     assert ctypes.sizeof(_ffi.Hit) == 16 == HIT_DTYPE.itemsize
     assert ctypes.sizeof(_ffi.IngestInfo) == 48
-    assert ctypes.sizeof(_ffi.BuildStats) == 128
+    assert ctypes.sizeof(_ffi.BuildStats) == 184
+    import numpy as np
+    assert np.dtype(_ffi.INGEST_INFO_DTYPE).itemsize == 48
+    lib = _ffi.load()
+    a, b, c = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
+    assert lib.pdg_struct_sizes(ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)) == 0
+    assert (a.value, b.value, c.value) == (ctypes.sizeof(_ffi.Hit), ctypes.sizeof(_ffi.IngestInfo),
+                                           ctypes.sizeof(_ffi.BuildStats))
 
 
 def test_no_device_fails_loudly(lib_built):

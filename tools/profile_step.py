@@ -16,8 +16,7 @@ def main():
     files = [(name, buf, torch.from_numpy(buf).cuda()) for name, buf, _ in synth.genomes(n)]
     for it in range(2):
         g.clear()
-        for name, host, d in files:
-            g._add_device(name, host, d)
+        g.add_fasta_batch(files)
         g.save()
         torch.cuda.synchronize()
     print(g.engine.counts(), g.engine.stats())
