@@ -162,7 +162,7 @@ def run_b200(a):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from prairiedog_b200 import B200Graph, synth
+    from prairiedog_b200 import B200Graph, synth, distributed
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -175,12 +175,7 @@ def run_b200(a):
         dist.init_process_group("nccl", device_id=dev)
 
     g = B200Graph(k=a.k, device=local)
-    if world > 1:
-        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
-        if rank == 0:
-            uid.copy_(torch.from_numpy(g.engine.comm_unique_id()))
-        dist.broadcast(uid, 0)
-        g.engine.comm_init(uid.cpu().numpy(), rank, world)
+    distributed.attach(g, dev)          # N > 1: every rank gets the NCCL id, opens the communicator
 
     # synthetic genomes of this rank: pinned host images and device-resident copies
     files, n_bases = [], 0
