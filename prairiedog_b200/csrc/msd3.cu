@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(256) m3_scan_chunks_kernel(uint32_t *__restric
 }
 
 // ---- pass 1: position tile -> records grouped by d3 ---------------------------------------------
+template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass1_kernel(const uint2 *__restrict__ packed,
                                                                  uint64_t packed_words, int k, ContigTable ct, M3Plan pl,
                                                                  const uint32_t *__restrict__ tile_info,
@@ -180,10 +181,11 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass1_kernel(const uint2 *__
         code[j] = m3_code_at(words[wi], words[wi + 1], lane, k);
         dg[j] = ((vm[wi] >> lane) & 1u) ? (code[j] >> sh3) : B3;
     }
-    m3_partition_tile<false>(sm, pos, code, dg, (int)B3, [sh3](uint32_t c) { return c >> sh3; }, out, nullptr);
+    m3_partition_tile<false, NBITS>(sm, pos, code, dg, (int)B3, [sh3](uint32_t c) { return c >> sh3; }, out, nullptr);
 }
 
 // ---- pass 2: range (chunk, d3) -> grouped by (d3, d2) --------------------------------------------
+template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass2_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ O1T,
                                                                  const uint32_t *__restrict__ O2,
@@ -216,12 +218,13 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass2_kernel(const uint2 *__
             code[j] = r.y;
             dg[j] = ok ? ((r.y >> b1) & m2) : B2;
         }
-        m3_partition_tile<false>(sm, pos, code, dg, (int)B2, [b1, m2](uint32_t cd) { return (cd >> b1) & m2; }, out,
+        m3_partition_tile<false, NBITS>(sm, pos, code, dg, (int)B2, [b1, m2](uint32_t cd) { return (cd >> b1) & m2; }, out,
                                  nullptr);
     }
 }
 
 // ---- pass 3: bucket (d3, d2): count d1, row starts, position column ------------------------------
+template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass3_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ base32,
                                                                  uint32_t *__restrict__ rowtab,
@@ -269,7 +272,7 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass3_kernel(const uint2 *__
             code[j] = r.y;
             dg[j] = ok ? (r.y & m1) : B1;
         }
-        m3_partition_tile<true>(sm, pos, code, dg, (int)B1, [m1](uint32_t cd) { return cd & m1; }, nullptr, out_pos);
+        m3_partition_tile<true, NBITS>(sm, pos, code, dg, (int)B1, [m1](uint32_t cd) { return cd & m1; }, nullptr, out_pos);
     }
 }
 
@@ -322,9 +325,9 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     static bool attr_set = false;
     if (!attr_set) {
         PDG_CUDA(cudaFuncSetAttribute(m3_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 1 << 16));
-        PDG_CUDA(cudaFuncSetAttribute(m3_pass1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
-        PDG_CUDA(cudaFuncSetAttribute(m3_pass2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
-        PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
+        PDG_CUDA(cudaFuncSetAttribute(m3_pass1_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
+        PDG_CUDA(cudaFuncSetAttribute(m3_pass2_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
+        PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
         attr_set = true;
     }
     const uint2 *packed = g->packed.as<uint2>();
@@ -352,14 +355,14 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     m3_scan_chunks_kernel<<<(cells + 255) / 256, 256, 0, s>>>(H12, pl.n_chunks, cells, base32);
     PDG_LAUNCHED(g);
     mark(2);
-    m3_pass1_kernel<<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, ct, pl, tile_info, H1T, g->recA.as<uint64_t>());
+    m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, ct, pl, tile_info, H1T, g->recA.as<uint64_t>());
     PDG_LAUNCHED(g);
     mark(3);
-    m3_pass2_kernel<<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem), s>>>(g->recA.as<uint2>(), pl, H1T, H12, base32,
+    m3_pass2_kernel<7><<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem), s>>>(g->recA.as<uint2>(), pl, H1T, H12, base32,
                                                                          g->recB.as<uint64_t>());
     PDG_LAUNCHED(g);
     mark(4);
-    m3_pass3_kernel<<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, base32, rowtab,
+    m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, base32, rowtab,
                                                               g->g_pos.as<uint32_t>());
     PDG_LAUNCHED(g);
     mark(5);

@@ -10,7 +10,6 @@ static constexpr int M3_ITEMS = 16;
 static constexpr int M3_TILE = M3_THREADS * M3_ITEMS;   // 4096 items per tile
 static constexpr int M3_WARP_TILE = 32 * M3_ITEMS;      // 512 consecutive items per warp
 static constexpr int M3_MAX_BINS = 256;
-static constexpr int M3_TAB = M3_MAX_BINS + 1;          // + the trash bin of items that are not records
 static constexpr int M3_TILE_WORDS = M3_TILE / 32;      // packed words per position tile
 static constexpr int kMsd3MaxBits = 22;                 // k <= 11: digits (<=7, <=7, <=8)
 static constexpr uint32_t M3_SIMPLE = 0x80000000u;      // tile_info flag: every window is a k-mer
@@ -18,11 +17,10 @@ static constexpr uint32_t M3_SIMPLE = 0x80000000u;      // tile_info flag: every
 // dynamic shared memory of one tile partition
 struct M3Smem {
     uint2 stage[M3_TILE];                    // the tile in sorted order: {position, code}
-    uint2 wtab[M3_WARPS][M3_TAB];            // per (warp, bin): {lane mask of the round, count / base}
+    uint32_t wcnt[M3_WARPS][M3_MAX_BINS];    // per (warp, bin): running count, then base inside the tile
     uint32_t delta[M3_MAX_BINS];             // global offset of the bin's run minus its start in stage
     uint32_t cursor[M3_MAX_BINS];            // global offset where this CTA writes the bin next
     uint32_t wsum[M3_WARPS];
-    uint32_t total;                          // records of the current tile
 };
 
 #ifdef __CUDACC__
@@ -52,34 +50,43 @@ __device__ __forceinline__ uint32_t m3_valid_word(const ContigTable &ct, uint64_
     return m;
 }
 
-// Stable partition of one tile by a digit.  Item j of lane l of warp w is tile element
-// w*512 + j*32 + l; dg[j] in [0, BINS) or BINS (= not a record, dropped; dg is clobbered).
-// pos[j] / code[j] is the record.  On entry sm.cursor[b] is the global offset of the first record of bin b of this
-// tile; on exit it has advanced by the tile's count (a CTA can walk consecutive tiles of a range).
-// OUT4: write the position to out4, else (code << 32 | position) to out8.
-// Ranking: every lane ORs its bit into the mask of its (warp, bin) entry, reads {mask, count}
-// back, and the lowest lane of each group folds the mask into the count -- no warp match
-// (MATCH.ANY sustains ~0.5 lanes/cycle/SM on sm_100, shared-memory atomics ~10).
-// Needs: wtab zeroed and a barrier since; leaves wtab zeroed and ends with a barrier.
-template <bool OUT4, typename DigitFn>
+// Stable partition of one tile by a digit of NBITS bits.  Item j of lane l of warp w is tile
+// element w*512 + j*32 + l; dg[j] in [0, BINS) or BINS (= not a record, dropped; dg is clobbered).
+// pos[j] / code[j] is the record.  On entry sm.cursor[b] is the global offset of the first record
+// of bin b of this tile; on exit it has advanced by the tile's count (a CTA can walk consecutive
+// tiles of a range).  OUT4: write the position to out4, else (code << 32 | position) to out8.
+// Ranking: the lanes of a round that share a digit find each other with NBITS ballots (no shared
+// memory, no MATCH.ANY -- ~0.5 lanes/clk/SM on sm_100); the per-(warp, bin) running count is one
+// 32-bit word read by all and advanced by the lowest lane of the group.  ncu on the earlier
+// {mask, count} table ranked by a shared-memory atomicOr: 22 of 37 shared-memory wavefronts per 32
+// records went into ranking (ATOMS.OR alone 9); this form needs ~7.
+// Needs: wcnt zeroed and a barrier since; leaves wcnt zeroed and ends with a barrier.
+template <bool OUT4, int NBITS, typename DigitFn>
 __device__ __forceinline__ void m3_partition_tile(M3Smem &sm, const uint32_t (&pos)[M3_ITEMS],
                                                   const uint32_t (&code)[M3_ITEMS], uint32_t (&dg)[M3_ITEMS],
                                                   const int BINS, DigitFn digit, uint64_t *__restrict__ out8,
                                                   uint32_t *__restrict__ out4) {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const uint32_t lt = (1u << lane) - 1u, bit = 1u << lane;
-    uint2 *wt = sm.wtab[w];
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t *wc = sm.wcnt[w];
     // dg[j] becomes digit | rank-within-(warp, bin) << 16 (one register per item instead of two)
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
-        uint2 *e = wt + dg[j];
-        atomicOr(&e->x, bit);
+        const uint32_t d = dg[j];
+        const bool ok = d != (uint32_t)BINS;
+        uint32_t peers = __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+        for (int b = 0; b < NBITS; ++b) {
+            const bool bit = (d >> b) & 1u;
+            const uint32_t m = __ballot_sync(0xffffffffu, bit);
+            peers &= bit ? m : ~m;
+        }
+        const uint32_t dd = ok ? d : 0u;
+        const uint32_t cnt = wc[dd];
+        const uint32_t below = peers & lt;
+        dg[j] = d | ((cnt + __popc(below)) << 16);
         __syncwarp();
-        const uint2 mc = *e;
-        const uint32_t below = mc.x & lt;
-        dg[j] |= (mc.y + __popc(below)) << 16;
-        __syncwarp();
-        if (below == 0) *e = make_uint2(0u, mc.y + __popc(mc.x));
+        if (ok && below == 0) wc[dd] = cnt + __popc(peers);
         __syncwarp();
     }
     __syncthreads();
@@ -87,7 +94,7 @@ __device__ __forceinline__ void m3_partition_tile(M3Smem &sm, const uint32_t (&p
     uint32_t c[M3_WARPS], tot = 0;
     if (tid < BINS) {
 #pragma unroll
-        for (int ww = 0; ww < M3_WARPS; ++ww) { c[ww] = sm.wtab[ww][tid].y; tot += c[ww]; }
+        for (int ww = 0; ww < M3_WARPS; ++ww) { c[ww] = sm.wcnt[ww][tid]; tot += c[ww]; }
     }
     uint32_t inc = tot;
 #pragma unroll
@@ -110,17 +117,17 @@ __device__ __forceinline__ void m3_partition_tile(M3Smem &sm, const uint32_t (&p
         sm.delta[tid] = cur - run;
         sm.cursor[tid] = cur + tot;
 #pragma unroll
-        for (int ww = 0; ww < M3_WARPS; ++ww) { sm.wtab[ww][tid].y = run; run += c[ww]; }
+        for (int ww = 0; ww < M3_WARPS; ++ww) { sm.wcnt[ww][tid] = run; run += c[ww]; }
     }
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const uint32_t d = dg[j] & 0xffffu;
-        if (d != (uint32_t)BINS) sm.stage[wt[d].y + (dg[j] >> 16)] = make_uint2(pos[j], code[j]);
+        if (d != (uint32_t)BINS) sm.stage[wc[d] + (dg[j] >> 16)] = make_uint2(pos[j], code[j]);
     }
     __syncthreads();
     // re-arm the table for the next tile while the stage drains
-    for (int i = tid; i < M3_WARPS * M3_TAB; i += M3_THREADS) (&sm.wtab[0][0])[i] = make_uint2(0u, 0u);
+    for (int i = tid; i < M3_WARPS * M3_MAX_BINS; i += M3_THREADS) (&sm.wcnt[0][0])[i] = 0u;
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const uint32_t s = j * M3_THREADS + tid;
@@ -134,7 +141,7 @@ __device__ __forceinline__ void m3_partition_tile(M3Smem &sm, const uint32_t (&p
 }
 
 __device__ __forceinline__ void m3_clear_table(M3Smem &sm) {
-    for (int i = threadIdx.x; i < M3_WARPS * M3_TAB; i += M3_THREADS) (&sm.wtab[0][0])[i] = make_uint2(0u, 0u);
+    for (int i = threadIdx.x; i < M3_WARPS * M3_MAX_BINS; i += M3_THREADS) (&sm.wcnt[0][0])[i] = 0u;
 }
 #endif
 
