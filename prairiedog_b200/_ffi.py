@@ -8,7 +8,7 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpdgpu.so")
+LIB_PATH = os.environ.get("PDG_LIBPDGPU", os.path.join(HERE, "libpdgpu.so"))   # override: tuning variants only
 
 PDG_OK = 0
 PDG_E_INVALID = -1

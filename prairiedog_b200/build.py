@@ -29,16 +29,19 @@ def needs_build():
     return any(os.path.getmtime(p) > t for p in _deps())
 
 
-def build_library(force=False, verbose=True):
-    if not force and not needs_build():
-        return LIB
+def build_library(force=False, verbose=True, extra_flags=(), out=None, tag=""):
+    """extra_flags / out / tag: tuning variants (tools/tune_msd3.py) built next to the product library."""
+    if out is None:
+        out = LIB
+        if not force and not needs_build():
+            return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     objs = []
     procs = []
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     for src in SOURCES:
-        obj = os.path.join(HERE, "build", src.replace(".cu", ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(HERE, "build", src.replace(".cu", tag + ".o"))
+        cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + ["-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             print(" ".join(cmd))
         procs.append((src, subprocess.Popen(cmd)))
@@ -46,11 +49,11 @@ def build_library(force=False, verbose=True):
     for src, p in procs:
         if p.wait() != 0:
             raise RuntimeError("nvcc failed on %s" % src)
-    cmd = [nvcc, "-shared", "--cudart", "static", "-o", LIB] + objs + ["-ldl"]
+    cmd = [nvcc, "-shared", "--cudart", "static", "-o", out] + objs + ["-ldl"]
     if verbose:
         print(" ".join(cmd))
     subprocess.check_call(cmd)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":

@@ -16,6 +16,7 @@
 #include "gindex.cuh"
 #include "msd3.cuh"
 #include <algorithm>
+#include <stdlib.h>
 
 namespace pdg {
 
@@ -116,18 +117,39 @@ __global__ void __launch_bounds__(1024) m3_base_kernel(const unsigned int *__res
     if (threadIdx.x == 0) base32[cells] = (uint32_t)carry;
 }
 
-// column d3 (one CTA): H1T[d3][tile] -> base3[d3] + exclusive prefix over tiles, in place
-__global__ void __launch_bounds__(1024) m3_scan_tiles_kernel(uint32_t *__restrict__ H1T, uint32_t n_tiles,
-                                                             const uint32_t *__restrict__ base32, int b2) {
-    uint32_t *col = H1T + (size_t)blockIdx.x * n_tiles;
-    uint64_t carry = base32[(size_t)blockIdx.x << b2];
-    for (uint32_t b = 0; b < n_tiles; b += 1024) {
-        const uint32_t i = b + threadIdx.x;
-        const uint64_t v = i < n_tiles ? col[i] : 0;
-        uint64_t tot;
-        const uint64_t ex = block_excl_scan(v, &tot);
-        if (i < n_tiles) col[i] = (uint32_t)(carry + ex);
-        carry += tot;
+// H1T[d3][tile] -> global offset of the first record of (tile, d3) in pass 1's output, in place.
+// One CTA per chunk, a warp per d3.  The range (chunk, d3) starts at
+//   base32[d3 << b2] + sum over d2 of (O2[chunk][d3, d2] - base32[d3, d2])
+// (O2 = H12 after m3_scan_chunks_kernel: records of cell (d3, d2) in earlier chunks), so every
+// (chunk, d3) pair scans its own tiles independently.
+__global__ void __launch_bounds__(256) m3_scan_tiles_kernel(uint32_t *__restrict__ H1T, M3Plan pl,
+                                                            const uint32_t *__restrict__ O2,
+                                                            const uint32_t *__restrict__ base32) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t B2 = 1u << pl.b2, B3 = 1u << pl.b3, c = blockIdx.x;
+    const uint32_t t0 = c * pl.ch, t1 = min(t0 + pl.ch, pl.n_tiles);
+    for (uint32_t d3 = w; d3 < B3; d3 += 8) {
+        uint32_t acc = 0;
+        for (uint32_t d2 = lane; d2 < B2; d2 += 32) {
+            const uint32_t cell = (d3 << pl.b2) | d2;
+            acc += O2[(size_t)c * (B3 * B2) + cell] - base32[cell];
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        uint32_t carry = base32[(size_t)d3 << pl.b2] + acc;
+        uint32_t *col = H1T + (size_t)d3 * pl.n_tiles;
+        for (uint32_t t = t0; t < t1; t += 32) {
+            const uint32_t i = t + lane;
+            const uint32_t v = i < t1 ? col[i] : 0u;
+            uint32_t inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += x;
+            }
+            if (i < t1) col[i] = carry + inc - v;
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+        }
     }
 }
 
@@ -152,7 +174,7 @@ __global__ void __launch_bounds__(256) m3_scan_chunks_kernel(uint32_t *__restric
 
 // ---- pass 1: position tile -> records grouped by d3 ---------------------------------------------
 template <int NBITS>
-__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass1_kernel(const uint2 *__restrict__ packed,
+__global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uint2 *__restrict__ packed,
                                                                  uint64_t packed_words, int k, ContigTable ct, M3Plan pl,
                                                                  const uint32_t *__restrict__ tile_info,
                                                                  const uint32_t *__restrict__ O1T,
@@ -166,27 +188,31 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass1_kernel(const uint2 *__
     const int sh3 = pl.b1 + pl.b2;
     const uint64_t w0 = (pl.base0 >> 5) + (uint64_t)tile * M3_TILE_WORDS;
     const uint32_t info = tile_info[tile];
-    if (tid < M3_TILE_WORDS + 2) words[tid] = w0 + tid < packed_words ? packed[w0 + tid] : make_uint2(0u, 0u);
+    for (int i = tid; i < M3_TILE_WORDS + 2; i += M3_THREADS)
+        words[i] = w0 + i < packed_words ? packed[w0 + i] : make_uint2(0u, 0u);
+    static_assert(M3_TILE_WORDS <= M3_THREADS, "one validity word per thread");
     if (tid < M3_TILE_WORDS)
         vm[tid] = (info & M3_SIMPLE) ? 0xffffffffu : m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, k);
-    if (tid < (int)B3) sm.cursor[tid] = O1T[(size_t)tid * pl.n_tiles + tile];
+    for (uint32_t b = tid; b < B3; b += M3_THREADS) sm.cursor[b] = O1T[(size_t)b * pl.n_tiles + tile];
     m3_clear_table(sm);
     __syncthreads();
     const uint32_t pbase = (uint32_t)(w0 << 5) + w * M3_WARP_TILE + lane;
-    uint32_t pos[M3_ITEMS], code[M3_ITEMS], dg[M3_ITEMS];
+    // only the digit stays in registers; the code is formed again from the staged words when the record is staged
+    uint32_t dg[M3_ITEMS];
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const int wi = w * M3_ITEMS + j;
-        pos[j] = pbase + 32 * j;
-        code[j] = m3_code_at(words[wi], words[wi + 1], lane, k);
-        dg[j] = ((vm[wi] >> lane) & 1u) ? (code[j] >> sh3) : B3;
+        dg[j] = ((vm[wi] >> lane) & 1u) ? (m3_code_at(words[wi], words[wi + 1], lane, k) >> sh3) : B3;
     }
-    m3_partition_tile<false, NBITS>(sm, pos, code, dg, (int)B3, [sh3](uint32_t c) { return c >> sh3; }, out, nullptr);
+    const uint2 *wrow = words + w * M3_ITEMS;
+    m3_partition_tile<false, NBITS>(
+        sm, [&](int j) { return make_uint2(pbase + 32 * j, m3_code_at(wrow[j], wrow[j + 1], lane, k)); }, dg, (int)B3,
+        [sh3](uint32_t c) { return c >> sh3; }, out, nullptr);
 }
 
 // ---- pass 2: range (chunk, d3) -> grouped by (d3, d2) --------------------------------------------
 template <int NBITS>
-__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass2_kernel(const uint2 *__restrict__ in, M3Plan pl,
+__global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ O1T,
                                                                  const uint32_t *__restrict__ O2,
                                                                  const uint32_t *__restrict__ base32,
@@ -200,7 +226,7 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass2_kernel(const uint2 *__
     const uint32_t end = (c + 1 < pl.n_chunks) ? O1T[(size_t)d3 * pl.n_tiles + (size_t)(c + 1) * pl.ch]
                                                 : base32[(size_t)(d3 + 1) << pl.b2];
     if (begin >= end) return;
-    if (tid < (int)B2) sm.cursor[tid] = O2[(size_t)c * (B3 * B2) + ((size_t)d3 << pl.b2) + tid];
+    for (uint32_t b = tid; b < B2; b += M3_THREADS) sm.cursor[b] = O2[(size_t)c * (B3 * B2) + ((size_t)d3 << pl.b2) + b];
     m3_clear_table(sm);
     __syncthreads();
     const int b1 = pl.b1;
@@ -209,23 +235,22 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass2_kernel(const uint2 *__
         const uint32_t tile_n = min((uint32_t)M3_TILE, end - t0);
         const uint2 *src = in + t0 + w * M3_WARP_TILE + lane;
         const uint32_t li0 = w * M3_WARP_TILE + lane;
-        uint32_t pos[M3_ITEMS], code[M3_ITEMS], dg[M3_ITEMS];
+        uint2 r[M3_ITEMS];
+        uint32_t dg[M3_ITEMS];
 #pragma unroll
         for (int j = 0; j < M3_ITEMS; ++j) {
             const bool ok = li0 + 32 * j < tile_n;
-            const uint2 r = ok ? src[32 * j] : make_uint2(0u, 0u);
-            pos[j] = r.x;
-            code[j] = r.y;
-            dg[j] = ok ? ((r.y >> b1) & m2) : B2;
+            r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
+            dg[j] = ok ? ((r[j].y >> b1) & m2) : B2;
         }
-        m3_partition_tile<false, NBITS>(sm, pos, code, dg, (int)B2, [b1, m2](uint32_t cd) { return (cd >> b1) & m2; }, out,
-                                 nullptr);
+        m3_partition_tile<false, NBITS>(sm, [&](int j) { return r[j]; }, dg, (int)B2,
+                                        [b1, m2](uint32_t cd) { return (cd >> b1) & m2; }, out, nullptr);
     }
 }
 
 // ---- pass 3: bucket (d3, d2): count d1, row starts, position column ------------------------------
 template <int NBITS>
-__global__ void __launch_bounds__(M3_THREADS, 3) m3_pass3_kernel(const uint2 *__restrict__ in, M3Plan pl,
+__global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ base32,
                                                                  uint32_t *__restrict__ rowtab,
                                                                  uint32_t *__restrict__ out_pos) {
@@ -235,14 +260,20 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass3_kernel(const uint2 *__
     const uint32_t B1 = 1u << pl.b1, m1 = B1 - 1, cell = blockIdx.x;
     const uint32_t begin = base32[cell], end = base32[cell + 1];
     // count d1 over the bucket (sm.delta doubles as the histogram)
-    sm.delta[tid] = 0;
+    for (int b = tid; b < M3_MAX_BINS; b += M3_THREADS) sm.delta[b] = 0;
     m3_clear_table(sm);
     __syncthreads();
     for (uint32_t i = begin + tid; i < end; i += M3_THREADS) atomicAdd(&sm.delta[in[i].y & m1], 1u);
     __syncthreads();
     {   // exclusive scan of the 256 counts -> first occurrence of every code of the bucket
-        const uint32_t v = sm.delta[tid];
-        uint32_t inc = v;
+        uint32_t v[M3_BPT], sum = 0;
+#pragma unroll
+        for (int i = 0; i < M3_BPT; ++i) {
+            const int b = tid * M3_BPT + i;
+            v[i] = b < M3_MAX_BINS ? sm.delta[b] : 0u;
+            sum += v[i];
+        }
+        uint32_t inc = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
@@ -250,29 +281,33 @@ __global__ void __launch_bounds__(M3_THREADS, 3) m3_pass3_kernel(const uint2 *__
         }
         if (lane == 31) sm.wsum[w] = inc;
         __syncthreads();
-        uint32_t base = begin;
+        uint32_t ex = begin + inc - sum;
 #pragma unroll
         for (int ww = 0; ww < M3_WARPS; ++ww)
-            if (ww < w) base += sm.wsum[ww];
-        const uint32_t ex = base + inc - v;
-        sm.cursor[tid] = ex;
-        if (tid < (int)B1) rowtab[((size_t)cell << pl.b1) + tid] = ex;
+            if (ww < w) ex += sm.wsum[ww];
+#pragma unroll
+        for (int i = 0; i < M3_BPT; ++i) {
+            const int b = tid * M3_BPT + i;
+            if (b < M3_MAX_BINS) sm.cursor[b] = ex;
+            if (b < (int)B1) rowtab[((size_t)cell << pl.b1) + b] = ex;
+            ex += v[i];
+        }
     }
     __syncthreads();
     for (uint32_t t0 = begin; t0 < end; t0 += M3_TILE) {
         const uint32_t tile_n = min((uint32_t)M3_TILE, end - t0);
         const uint2 *src = in + t0 + w * M3_WARP_TILE + lane;
         const uint32_t li0 = w * M3_WARP_TILE + lane;
-        uint32_t pos[M3_ITEMS], code[M3_ITEMS], dg[M3_ITEMS];
+        uint2 r[M3_ITEMS];
+        uint32_t dg[M3_ITEMS];
 #pragma unroll
         for (int j = 0; j < M3_ITEMS; ++j) {
             const bool ok = li0 + 32 * j < tile_n;
-            const uint2 r = ok ? src[32 * j] : make_uint2(0u, 0u);
-            pos[j] = r.x;
-            code[j] = r.y;
-            dg[j] = ok ? (r.y & m1) : B1;
+            r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
+            dg[j] = ok ? (r[j].y & m1) : B1;
         }
-        m3_partition_tile<true, NBITS>(sm, pos, code, dg, (int)B1, [m1](uint32_t cd) { return cd & m1; }, nullptr, out_pos);
+        m3_partition_tile<true, NBITS>(sm, [&](int j) { return r[j]; }, dg, (int)B1,
+                                       [m1](uint32_t cd) { return cd & m1; }, nullptr, out_pos);
     }
 }
 
@@ -303,7 +338,9 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     pl.base0 = hc.pos0 & ~31ULL;
     pl.n_tiles = (uint32_t)((hc.pos1 - pl.base0 + M3_TILE - 1) / M3_TILE);
     const uint32_t B3 = 1u << pl.b3, cells = 1u << (pl.b3 + pl.b2);
-    pl.ch = std::max<uint32_t>(1, (3500u * B3) / M3_TILE);   // ranges of pass 2 average ~3500 records
+    // ranges of pass 2 average ~m3_range records (a few tiles each: little padding, still >> SMs ranges)
+    static const uint32_t m3_range = getenv("PDG_M3_RANGE") ? (uint32_t)atoi(getenv("PDG_M3_RANGE")) : 6000u;
+    pl.ch = std::max<uint32_t>(1, (uint32_t)(((uint64_t)m3_range * B3) / M3_TILE));
     pl.n_chunks = (pl.n_tiles + pl.ch - 1) / pl.ch;
     const uint64_t n_codes = 1ULL << (2 * k);
 
@@ -350,9 +387,9 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     mark(1);
     m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32);
     PDG_LAUNCHED(g);
-    m3_scan_tiles_kernel<<<B3, 1024, 0, s>>>(H1T, pl.n_tiles, base32, pl.b2);
-    PDG_LAUNCHED(g);
     m3_scan_chunks_kernel<<<(cells + 255) / 256, 256, 0, s>>>(H12, pl.n_chunks, cells, base32);
+    PDG_LAUNCHED(g);
+    m3_scan_tiles_kernel<<<pl.n_chunks, 256, 0, s>>>(H1T, pl, H12, base32);
     PDG_LAUNCHED(g);
     mark(2);
     m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, ct, pl, tile_info, H1T, g->recA.as<uint64_t>());

@@ -4,12 +4,19 @@
 
 namespace pdg {
 
-static constexpr int M3_THREADS = 256;
+#ifndef M3_CFG_THREADS
+#define M3_CFG_THREADS 256   /* tools/tune_msd3.py: 256 threads x 8 items, 5 CTAs/SM was the fastest of 8 shapes on B200 */
+#define M3_CFG_ITEMS 8
+#define M3_CFG_MINB 5
+#endif
+static constexpr int M3_THREADS = M3_CFG_THREADS;
 static constexpr int M3_WARPS = M3_THREADS / 32;
-static constexpr int M3_ITEMS = 16;
-static constexpr int M3_TILE = M3_THREADS * M3_ITEMS;   // 4096 items per tile
-static constexpr int M3_WARP_TILE = 32 * M3_ITEMS;      // 512 consecutive items per warp
+static constexpr int M3_ITEMS = M3_CFG_ITEMS;
+static constexpr int M3_MINB = M3_CFG_MINB;                       // CTAs per SM the pass kernels are compiled for
+static constexpr int M3_TILE = M3_THREADS * M3_ITEMS;   // items per tile
+static constexpr int M3_WARP_TILE = 32 * M3_ITEMS;      // consecutive items per warp
 static constexpr int M3_MAX_BINS = 256;
+static constexpr int M3_BPT = (M3_MAX_BINS + M3_THREADS - 1) / M3_THREADS;   // bins a thread owns in the scan
 static constexpr int M3_TILE_WORDS = M3_TILE / 32;      // packed words per position tile
 static constexpr int kMsd3MaxBits = 22;                 // k <= 11: digits (<=7, <=7, <=8)
 static constexpr uint32_t M3_SIMPLE = 0x80000000u;      // tile_info flag: every window is a k-mer
@@ -51,8 +58,8 @@ __device__ __forceinline__ uint32_t m3_valid_word(const ContigTable &ct, uint64_
 }
 
 // Stable partition of one tile by a digit of NBITS bits.  Item j of lane l of warp w is tile
-// element w*512 + j*32 + l; dg[j] in [0, BINS) or BINS (= not a record, dropped; dg is clobbered).
-// pos[j] / code[j] is the record.  On entry sm.cursor[b] is the global offset of the first record
+// element w*32*M3_ITEMS + j*32 + l; dg[j] in [0, BINS) or BINS (= not a record, dropped; dg is clobbered).
+// rec(j) returns the record {position, code} of item j (called once, for kept items).  On entry sm.cursor[b] is the global offset of the first record
 // of bin b of this tile; on exit it has advanced by the tile's count (a CTA can walk consecutive
 // tiles of a range).  OUT4: write the position to out4, else (code << 32 | position) to out8.
 // Ranking: the lanes of a round that share a digit find each other with NBITS ballots (no shared
@@ -61,42 +68,60 @@ __device__ __forceinline__ uint32_t m3_valid_word(const ContigTable &ct, uint64_
 // {mask, count} table ranked by a shared-memory atomicOr: 22 of 37 shared-memory wavefronts per 32
 // records went into ranking (ATOMS.OR alone 9); this form needs ~7.
 // Needs: wcnt zeroed and a barrier since; leaves wcnt zeroed and ends with a barrier.
-template <bool OUT4, int NBITS, typename DigitFn>
-__device__ __forceinline__ void m3_partition_tile(M3Smem &sm, const uint32_t (&pos)[M3_ITEMS],
-                                                  const uint32_t (&code)[M3_ITEMS], uint32_t (&dg)[M3_ITEMS],
+// One digit bit of the ranking ballots: lanes whose bit equals mine stay in `same` / never enter `other`.
+__device__ __forceinline__ void m3_vote_bit(uint32_t d, uint32_t bitmask, uint32_t &same, uint32_t &other) {
+    asm("{\n\t.reg .pred p;\n\t.reg .b32 m, t;\n\t"
+        "and.b32 t, %2, %3;\n\t"
+        "setp.ne.u32 p, t, 0;\n\t"
+        "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
+        "@p and.b32 %0, %0, m;\n\t"
+        "@!p or.b32 %1, %1, m;\n\t}"
+        : "+r"(same), "+r"(other) : "r"(d), "r"(bitmask));
+}
+
+template <bool OUT4, int NBITS, typename RecFn, typename DigitFn>
+__device__ __forceinline__ void m3_partition_tile(M3Smem &sm, RecFn rec, uint32_t (&dg)[M3_ITEMS],
                                                   const int BINS, DigitFn digit, uint64_t *__restrict__ out8,
                                                   uint32_t *__restrict__ out4) {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t *wc = sm.wcnt[w];
-    // dg[j] becomes digit | rank-within-(warp, bin) << 16 (one register per item instead of two)
+    // phase 1 (registers and ballots only, no memory: the items overlap freely): the lanes of a
+    // round that share a digit.  dg[j] becomes digit | lanes-below << 9 | group size << 15 | leader << 21
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const uint32_t d = dg[j];
         const bool ok = d != (uint32_t)BINS;
-        uint32_t peers = __ballot_sync(0xffffffffu, ok);
+        uint32_t same = __ballot_sync(0xffffffffu, ok), other = 0u;
 #pragma unroll
-        for (int b = 0; b < NBITS; ++b) {
-            const bool bit = (d >> b) & 1u;
-            const uint32_t m = __ballot_sync(0xffffffffu, bit);
-            peers &= bit ? m : ~m;
-        }
-        const uint32_t dd = ok ? d : 0u;
+        for (int b = 0; b < NBITS; ++b) m3_vote_bit(d, 1u << b, same, other);
+        const uint32_t peers = same & ~other, below = peers & lt;
+        dg[j] = d | (__popc(below) << 9) | (__popc(peers) << 15) | ((ok && below == 0u) ? (1u << 21) : 0u);
+    }
+    // phase 2: running count of the (warp, bin) pair; dg[j] becomes digit | rank << 16
+#pragma unroll
+    for (int j = 0; j < M3_ITEMS; ++j) {
+        const uint32_t x = dg[j], d = x & 0x1ffu, dd = d & (M3_MAX_BINS - 1);
         const uint32_t cnt = wc[dd];
-        const uint32_t below = peers & lt;
-        dg[j] = d | ((cnt + __popc(below)) << 16);
+        dg[j] = d | ((cnt + ((x >> 9) & 63u)) << 16);
         __syncwarp();
-        if (ok && below == 0) wc[dd] = cnt + __popc(peers);
+        if (x >> 21) wc[dd] = cnt + ((x >> 15) & 63u);
         __syncwarp();
     }
     __syncthreads();
-    // bin `tid`: counts of the warps -> exclusive bases, tile count
-    uint32_t c[M3_WARPS], tot = 0;
-    if (tid < BINS) {
+    // bins tid*BPT .. tid*BPT+BPT-1: counts of the warps -> exclusive bases, tile count
+    uint32_t c[M3_BPT][M3_WARPS], tot[M3_BPT], sum = 0;
 #pragma unroll
-        for (int ww = 0; ww < M3_WARPS; ++ww) { c[ww] = sm.wcnt[ww][tid]; tot += c[ww]; }
+    for (int i = 0; i < M3_BPT; ++i) {
+        const int b = tid * M3_BPT + i;
+        tot[i] = 0;
+        if (b < BINS) {
+#pragma unroll
+            for (int ww = 0; ww < M3_WARPS; ++ww) { c[i][ww] = sm.wcnt[ww][b]; tot[i] += c[i][ww]; }
+        }
+        sum += tot[i];
     }
-    uint32_t inc = tot;
+    uint32_t inc = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
@@ -111,19 +136,23 @@ __device__ __forceinline__ void m3_partition_tile(M3Smem &sm, const uint32_t (&p
         if (ww < w) base += v;
         all += v;
     }
-    if (tid < BINS) {
-        uint32_t run = base + inc - tot;           // start of the bin inside the tile
-        const uint32_t cur = sm.cursor[tid];
-        sm.delta[tid] = cur - run;
-        sm.cursor[tid] = cur + tot;
+    uint32_t run = base + inc - sum;               // start of this thread's first bin inside the tile
 #pragma unroll
-        for (int ww = 0; ww < M3_WARPS; ++ww) { sm.wcnt[ww][tid] = run; run += c[ww]; }
+    for (int i = 0; i < M3_BPT; ++i) {
+        const int b = tid * M3_BPT + i;
+        if (b < BINS) {
+            const uint32_t cur = sm.cursor[b];
+            sm.delta[b] = cur - run;
+            sm.cursor[b] = cur + tot[i];
+#pragma unroll
+            for (int ww = 0; ww < M3_WARPS; ++ww) { sm.wcnt[ww][b] = run; run += c[i][ww]; }
+        }
     }
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const uint32_t d = dg[j] & 0xffffu;
-        if (d != (uint32_t)BINS) sm.stage[wc[d] + (dg[j] >> 16)] = make_uint2(pos[j], code[j]);
+        if (d != (uint32_t)BINS) sm.stage[wc[d] + (dg[j] >> 16)] = rec(j);
     }
     __syncthreads();
     // re-arm the table for the next tile while the stage drains
