@@ -24,7 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "genome_bp_per_sec_into_pangenome_graph_k11"
+METRIC = "genome_bp_per_sec_into_pangenome_graph_k11"      # k filled in from --k (default 11)
 UNIT = "bp/s"
 
 
@@ -304,7 +304,9 @@ def kernel_table(st, k, peak):
 
 
 def main():
+    global METRIC
     a = parse_args()
+    METRIC = "genome_bp_per_sec_into_pangenome_graph_k%d" % a.k
     if a.impl == "reference":
         run_reference(a)
     else:
