@@ -97,7 +97,8 @@ int finalize(pdg_graph *g, int flags) {
     if (g->world > 1) {
         // K5: hash-partitioned exchange of the node keys; every rank ends with the global table
         uint64_t n_glob = 0;
-        const int rc = comm_global_nodes(g, g->u_codes, n_local, 64, &n_glob);
+        // opaque node keys of the explicit part carry bit 63; clean k-mer codes need 2k bits
+        const int rc = comm_global_nodes(g, g->u_codes, n_local, g->x_n_nodes ? 64 : 2 * k, &n_glob);
         if (rc != PDG_OK) return rc;
         g->u_codes = g->u_codes_buf.as<uint64_t>();
         g->n_nodes = n_glob;

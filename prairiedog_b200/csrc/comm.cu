@@ -107,6 +107,55 @@ __global__ void compact_keys_kernel(const uint64_t *__restrict__ keys, const uin
 
 static inline unsigned gridf(uint64_t n) { return (unsigned)((n + 255) / 256); }
 
+// Small k (every rank holds a presence bitmap over all 4^k codes and no explicit nodes): the global
+// node set is the OR of the ranks' bitmaps -- one ncclAllGather of 4^k / 8 bytes per rank (512 KiB at
+// k = 11), an OR + popcount pass, a prefix sum and an expansion back to sorted codes.
+__global__ void or_bitmaps_kernel(const uint32_t *__restrict__ all, int world, uint64_t n_words,
+                                  uint32_t *__restrict__ out, uint32_t *__restrict__ cnt) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_words) return;
+    uint32_t m = 0;
+    for (int p = 0; p < world; ++p) m |= all[(size_t)p * n_words + i];
+    out[i] = m;
+    cnt[i] = __popc(m);
+}
+__global__ void expand_bitmap_kernel(const uint32_t *__restrict__ bm, const uint32_t *__restrict__ prefix,
+                                     uint64_t n_words, uint64_t *__restrict__ codes) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_words) return;
+    uint32_t m = bm[i], at = prefix[i];
+    while (m) {
+        const int b = __ffs(m) - 1;
+        m &= m - 1;
+        codes[at++] = (i << 5) | (uint64_t)b;
+    }
+}
+
+static int comm_global_nodes_bitmap(pdg_graph *g, NcclApi *api, uint64_t *n_global) {
+    cudaStream_t s = g->stream;
+    ncclComm_t comm = reinterpret_cast<ncclComm_t>(g->nccl_comm);
+    const int W = g->world;
+    const uint64_t nw = g->bitmap_words;
+    g->c_all.reserve((size_t)W * nw * 4, s);
+    g->c_all2.reserve(nw * 4, s);
+    g->c_tmp.reserve(nw * 4, s);
+    g->c_own.reserve((nw + 1) * 4, s);
+    PDG_NCCL(api, api->AllGather(g->bitmap.p, g->c_all.p, nw, ncclUint32, comm, s));
+    or_bitmaps_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, s>>>(g->c_all.as<uint32_t>(), W, nw, g->c_all2.as<uint32_t>(),
+                                                                  g->c_tmp.as<uint32_t>());
+    PDG_LAUNCHED(g);
+    exclusive_scan_u32_u32(g->c_tmp.as<uint32_t>(), g->c_own.as<uint32_t>(), nw, g);
+    uint32_t n32 = 0;
+    PDG_CUDA(cudaMemcpyAsync(&n32, g->c_own.as<uint32_t>() + nw, 4, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    g->u_codes_buf.reserve(std::max<size_t>((size_t)n32 * 8, 16), s);
+    expand_bitmap_kernel<<<(unsigned)((nw + 255) / 256), 256, 0, s>>>(g->c_all2.as<uint32_t>(), g->c_own.as<uint32_t>(), nw,
+                                                                     g->u_codes_buf.as<uint64_t>());
+    PDG_LAUNCHED(g);
+    *n_global = n32;
+    return PDG_OK;
+}
+
 // In: d_local holds this rank's sorted unique codes (n_loc of them; may alias g->u_codes_buf).
 // Out: g->u_codes_buf holds the global sorted unique table, *n_global its size.
 int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int key_bits, uint64_t *n_global) {
@@ -120,8 +169,30 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
     ncclComm_t comm = reinterpret_cast<ncclComm_t>(g->nccl_comm);
     const int W = g->world, R = g->rank;
 
+    // 0. agree on the path: every rank reports {words of its presence bitmap or 0, key bits it needs}
+    {
+        g->c_counts.reserve(2 * 64 * 8, s);
+        g->c_all_counts.reserve((size_t)64 * 64 * 8, s);
+        const bool bm_ok = g->have_bitmap && g->x_n_nodes == 0 && d_local == g->g_codes.as<uint64_t>() &&
+                           g->bitmap_words * 4 * (uint64_t)W <= (256ull << 20);
+        const uint64_t mine[2] = {bm_ok ? g->bitmap_words : 0, (uint64_t)key_bits};
+        PDG_CUDA(cudaMemcpyAsync(g->c_counts.p, mine, 16, cudaMemcpyHostToDevice, s));
+        PDG_NCCL(api, api->AllGather(g->c_counts.p, g->c_all_counts.p, 2, ncclUint64, comm, s));
+        std::vector<uint64_t> all(2 * W);
+        PDG_CUDA(cudaMemcpyAsync(all.data(), g->c_all_counts.p, 2 * W * 8, cudaMemcpyDeviceToHost, s));
+        PDG_CUDA(cudaStreamSynchronize(s));
+        bool use_bitmap = mine[0] != 0;
+        for (int p = 0; p < W; ++p) {
+            use_bitmap = use_bitmap && all[2 * p] == mine[0];
+            key_bits = std::max<int>(key_bits, (int)all[2 * p + 1]);
+        }
+        // a rank that cannot take the bitmap path reports 0, so the decision is the same everywhere
+        for (int p = 0; p < W; ++p) use_bitmap = use_bitmap && all[2 * p] != 0;
+        if (use_bitmap) return comm_global_nodes_bitmap(g, api, n_global);
+    }
+
     // 1. bucket the local unique codes by owner
-    DevBuf d_counts, d_all_counts, d_send, d_recv;
+    DevBuf &d_counts = g->c_counts, &d_all_counts = g->c_all_counts, &d_send = g->c_send, &d_recv = g->c_recv;
     d_counts.reserve(2 * W * 8, s);
     d_all_counts.reserve((size_t)W * W * 8, s);
     PDG_CUDA(cudaMemsetAsync(d_counts.p, 0, 2 * W * 8, s));
@@ -161,7 +232,7 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
 
     // 3. owner: sort + run-length compaction of what was received
     uint64_t n_own = 0;
-    DevBuf d_own, d_tmp;
+    DevBuf &d_own = g->c_own, &d_tmp = g->c_tmp;
     d_own.reserve(std::max<size_t>(n_recv * 8, 16), s);
     if (n_recv) {
         d_tmp.reserve(n_recv * 8, s);
@@ -187,7 +258,7 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
     std::vector<uint64_t> own_off(W + 1, 0);
     for (int p = 0; p < W; ++p) own_off[p + 1] = own_off[p] + own_counts[p];
     const uint64_t n_glob = own_off[W];
-    DevBuf d_all, d_all2;
+    DevBuf &d_all = g->c_all, &d_all2 = g->c_all2;
     d_all.reserve(std::max<size_t>(n_glob * 8, 16), s);
     d_all2.reserve(std::max<size_t>(n_glob * 8, 16), s);
     PDG_NCCL(api, api->GroupStart());

@@ -172,6 +172,7 @@ struct pdg_graph {
     uint64_t ingest_bytes = 0, ingest_launches = 0;
 
     // ---- multi GPU ----
+    pdg::DevBuf c_counts, c_all_counts, c_send, c_recv, c_own, c_tmp, c_all, c_all2;   // comm.cu scratch
     void *nccl_comm = nullptr;
     int rank = 0, world = 1;
 };
