@@ -1,0 +1,81 @@
+"""`-m gpu`: parity at E. coli scale.  Full-size genomes (5 Mbp, 200 contigs) against the C oracle bit for
+bit (index arrays, checksums), and size-independent properties at larger sizes: the order-independent
+edge checksum is additive over disjoint genome sets, rows are sorted, every indexed position spells
+the k-mer of its row, batch order of independent files does not change the canonical graph."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _need_gpu(lib_built):
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+
+
+def _genomes(n, first=0, n_bases=5_000_000, n_contigs=200):
+    from prairiedog_b200 import synth
+    return [(name, buf, None) for name, buf, _ in synth.genomes(n, n_bases=n_bases, n_contigs=n_contigs, first=first)]
+
+
+def _build(k, files, first_type=0):
+    from prairiedog_b200 import B200Graph
+    g = B200Graph(k=k)
+    g._next_type = first_type         # edge labels are hashed by type id: keep ids as in the whole graph
+    counts = g.add_fasta_batch(files)
+    g.save()
+    return g, counts
+
+
+@pytest.mark.parametrize("k", [11, 13, 31])
+def test_full_size_genomes_match_the_c_oracle(k):
+    from oracle.c_oracle import COracle
+    files = _genomes(2)
+    g, _ = _build(k, files)
+    o = COracle(k)
+    for _, buf, _ in files:
+        o.add_fasta_bytes(buf)
+    o.build()
+    assert g.engine.counts() == o.counts()
+    assert g.engine.checksum() == o.checksum()
+    for got, want in zip(g.engine.export_index(), o.index()):
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("k", [11, 31])
+def test_edge_checksum_is_additive_and_rows_are_sorted(k):
+    files = _genomes(12)
+    whole, counts = _build(k, files)
+    a, _ = _build(k, files[:5])
+    b, _ = _build(k, files[5:], first_type=a._next_type)
+    na, ea, ka = a.engine.counts()
+    nb, eb, kb = b.engine.counts()
+    nw, ew, kw = whole.engine.counts()
+    assert (ew, kw) == (ea + eb, ka + kb) and kw == sum(counts)
+    assert max(na, nb) <= nw <= na + nb
+    mask = (1 << 64) - 1
+    assert whole.engine.checksum()[1] == (a.engine.checksum()[1] + b.engine.checksum()[1]) & mask
+    codes, rowptr, pos = whole.engine.export_index()
+    assert codes.size == nw and int(rowptr[-1]) == kw == pos.size
+    assert (np.diff(codes.astype(np.int64)) > 0).all() if k <= 31 else True
+    assert (np.diff(rowptr.astype(np.int64)) > 0).all()              # no empty row
+    d = np.diff(pos.astype(np.int64))
+    d[rowptr[1:-1].astype(np.int64) - 1] = 1                          # row boundaries may go down
+    assert (d > 0).all()                                              # positions ascend inside every row
+    # sampled rows: the k-mer at every position of the row is the row's code
+    rng = np.random.default_rng(7)
+    for r in rng.integers(0, nw, size=200).tolist():
+        ps = pos[int(rowptr[r]):int(rowptr[r + 1])][:4]
+        for p in ps.tolist():
+            assert int(whole.engine.emit_codes(p, k)[0]) == int(codes[r])
+
+
+def test_batch_order_does_not_change_the_graph():
+    """type ids follow load order, labels do not: the canonical (string) forms must agree"""
+    files = _genomes(3, n_bases=150_000, n_contigs=10)
+    g1, _ = _build(11, files)
+    g2, _ = _build(11, files[::-1])
+    assert g1.engine.checksum()[0] == g2.engine.checksum()[0]          # node set checksum
+    assert np.array_equal(g1.engine.export_nodes(), g2.engine.export_nodes())
+    assert g1.canonical() == g2.canonical()
