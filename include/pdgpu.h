@@ -100,6 +100,7 @@ typedef struct pdg_build_stats {
     /* CUDA-event times of the last pdg_ingest_fasta_batch: pass A (summaries; in host mode it
      * includes waiting for the copies), pass B (scan), pass C (emit + header hashes) */
     float ms_ingest_a, ms_ingest_b, ms_ingest_c, pad3;
+    uint64_t sort_groups;       /* groups of positions the k <= 11 index was staged in (1 unless pipelined) */
     uint64_t ingest_bytes;      /* bytes parsed by the last pdg_ingest_fasta_batch */
     uint64_t ingest_launches;
 } pdg_build_stats;

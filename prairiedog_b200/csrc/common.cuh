@@ -153,7 +153,11 @@ struct pdg_graph {
     const uint64_t *u_codes = nullptr;   // points at g_codes, x_codes or u_codes_buf
 
     // ---- scratch ----
-    pdg::DevBuf m3_tile_info;
+    pdg::DevBuf m3_tile_info, m3_gbase;   // msd3.cu: per-tile contig info; per-group cell bases + record offsets
+    struct M3Group { uint64_t pos0, pos1, rec_off; };
+    std::vector<M3Group> m3_groups;      // groups staged since msd3_reserve
+    uint32_t m3_max_groups = 0;
+    uint64_t m3_pos_lo = 0;
     pdg::DevBuf recA, recB, scratch0, scratch1, scratch2, status, hist;
     pdg::DevBuf q_a, q_b, q_cnt, q_cnt_g, q_off, q_hits, small;
     uint64_t q_n = 0, q_total = 0;

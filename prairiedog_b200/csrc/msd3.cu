@@ -249,8 +249,26 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uin
 }
 
 // ---- pass 3: bucket (d3, d2): count d1, row starts, position column ------------------------------
+// The bucket of a cell is the concatenation, in group order, of the cell's segment of every group
+// (a group = one run of passes 1-2 over a range of positions, see msd3_stage_group):
+// segment g = in[goff[g] + gbase[g][cell] .. goff[g] + gbase[g][cell + 1]).
+// tot[cell] = records of the cell over all groups (input of the base scan)
+__global__ void m3_cell_totals_kernel(const uint32_t *__restrict__ gbase, uint32_t n_groups, uint32_t cells,
+                                      unsigned int *__restrict__ tot) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cells) return;
+    uint32_t t = 0;
+    for (uint32_t g = 0; g < n_groups; ++g) {
+        const uint32_t *gb = gbase + (size_t)g * (cells + 1);
+        t += gb[c + 1] - gb[c];
+    }
+    tot[c] = t;
+}
+
 template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uint2 *__restrict__ in, M3Plan pl,
+                                                                 const uint32_t *__restrict__ gbase,
+                                                                 const uint32_t *__restrict__ goff, uint32_t n_groups,
                                                                  const uint32_t *__restrict__ base32,
                                                                  uint32_t *__restrict__ rowtab,
                                                                  uint32_t *__restrict__ out_pos) {
@@ -258,12 +276,17 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uin
     M3Smem &sm = *reinterpret_cast<M3Smem *>(m3_raw);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t B1 = 1u << pl.b1, m1 = B1 - 1, cell = blockIdx.x;
-    const uint32_t begin = base32[cell], end = base32[cell + 1];
+    const uint32_t cells1 = (1u << (pl.b3 + pl.b2)) + 1;
+    const uint32_t begin = base32[cell];
     // count d1 over the bucket (sm.delta doubles as the histogram)
     for (int b = tid; b < M3_MAX_BINS; b += M3_THREADS) sm.delta[b] = 0;
     m3_clear_table(sm);
     __syncthreads();
-    for (uint32_t i = begin + tid; i < end; i += M3_THREADS) atomicAdd(&sm.delta[in[i].y & m1], 1u);
+    for (uint32_t gi = 0; gi < n_groups; ++gi) {
+        const uint32_t *gb = gbase + (size_t)gi * cells1;
+        const uint32_t sb = goff[gi] + gb[cell], se = goff[gi] + gb[cell + 1];
+        for (uint32_t i = sb + tid; i < se; i += M3_THREADS) atomicAdd(&sm.delta[in[i].y & m1], 1u);
+    }
     __syncthreads();
     {   // exclusive scan of the 256 counts -> first occurrence of every code of the bucket
         uint32_t v[M3_BPT], sum = 0;
@@ -294,20 +317,24 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uin
         }
     }
     __syncthreads();
-    for (uint32_t t0 = begin; t0 < end; t0 += M3_TILE) {
-        const uint32_t tile_n = min((uint32_t)M3_TILE, end - t0);
-        const uint2 *src = in + t0 + w * M3_WARP_TILE + lane;
-        const uint32_t li0 = w * M3_WARP_TILE + lane;
-        uint2 r[M3_ITEMS];
-        uint32_t dg[M3_ITEMS];
+    for (uint32_t gi = 0; gi < n_groups; ++gi) {
+        const uint32_t *gb = gbase + (size_t)gi * cells1;
+        const uint32_t sb = goff[gi] + gb[cell], se = goff[gi] + gb[cell + 1];
+        for (uint32_t t0 = sb; t0 < se; t0 += M3_TILE) {
+            const uint32_t tile_n = min((uint32_t)M3_TILE, se - t0);
+            const uint2 *src = in + t0 + w * M3_WARP_TILE + lane;
+            const uint32_t li0 = w * M3_WARP_TILE + lane;
+            uint2 r[M3_ITEMS];
+            uint32_t dg[M3_ITEMS];
 #pragma unroll
-        for (int j = 0; j < M3_ITEMS; ++j) {
-            const bool ok = li0 + 32 * j < tile_n;
-            r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
-            dg[j] = ok ? (r[j].y & m1) : B1;
+            for (int j = 0; j < M3_ITEMS; ++j) {
+                const bool ok = li0 + 32 * j < tile_n;
+                r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
+                dg[j] = ok ? (r[j].y & m1) : B1;
+            }
+            m3_partition_tile<true, NBITS>(sm, [&](int j) { return r[j]; }, dg, (int)B1,
+                                           [m1](uint32_t cd) { return cd & m1; }, nullptr, out_pos);
         }
-        m3_partition_tile<true, NBITS>(sm, [&](int j) { return r[j]; }, dg, (int)B1,
-                                       [m1](uint32_t cd) { return cd & m1; }, nullptr, out_pos);
     }
 }
 
@@ -327,38 +354,46 @@ __global__ void m3_compact_rows_kernel(const uint32_t *__restrict__ rowtab, cons
     if (i == 0) rowptr[rank[n_codes]] = rowtab[n_codes];
 }
 
-void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
-    cudaStream_t s = g->stream;
-    const int k = g->k;
-    const uint64_t n = hc.n_kmers;
+// ---- host -----------------------------------------------------------------------------------------
+// The build runs in three steps so that FASTA batches can be staged while later files are still
+// being copied (ingest_batch.cu):
+//   msd3_reserve      buffers for positions [pos_lo, pos_hi) and up to max_groups groups
+//   msd3_stage_group  histogram + scans + passes 1-2 over one range of positions (a group); its
+//                     records land in recB at rec_off, grouped by (d3, d2); its cell bases are kept
+//   msd3_finish       pass 3 over the cells (segments of all groups in order) + rows
+static M3Plan m3_plan(int k, uint64_t pos0, uint64_t pos1) {
     M3Plan pl{};
     pl.b1 = std::min(8, 2 * k);
     pl.b2 = std::min(7, 2 * k - pl.b1);
     pl.b3 = 2 * k - pl.b1 - pl.b2;
-    pl.base0 = hc.pos0 & ~31ULL;
-    pl.n_tiles = (uint32_t)((hc.pos1 - pl.base0 + M3_TILE - 1) / M3_TILE);
-    const uint32_t B3 = 1u << pl.b3, cells = 1u << (pl.b3 + pl.b2);
+    pl.base0 = pos0 & ~31ULL;
+    pl.n_tiles = (uint32_t)((pos1 - pl.base0 + M3_TILE - 1) / M3_TILE);
     // ranges of pass 2 average ~m3_range records (a few tiles each: little padding, still >> SMs ranges)
     static const uint32_t m3_range = getenv("PDG_M3_RANGE") ? (uint32_t)atoi(getenv("PDG_M3_RANGE")) : 6000u;
-    pl.ch = std::max<uint32_t>(1, (uint32_t)(((uint64_t)m3_range * B3) / M3_TILE));
+    pl.ch = std::max<uint32_t>(1, (uint32_t)(((uint64_t)m3_range << pl.b3) / M3_TILE));
     pl.n_chunks = (pl.n_tiles + pl.ch - 1) / pl.ch;
-    const uint64_t n_codes = 1ULL << (2 * k);
+    return pl;
+}
 
-    g->status.reserve((size_t)B3 * pl.n_tiles * 4, s);                 // H1T -> O1T
-    g->scratch1.reserve(std::max<size_t>((size_t)pl.n_chunks * cells * 4, (n_codes + 1) * 4), s);   // H12 -> O2, later ranks
-    g->hist.reserve((size_t)(2 * cells + 2) * 4, s);                    // tot32 | base32
-    g->scratch0.reserve((n_codes + 1) * 4, s);                          // row starts of every code
+void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_groups) {
+    cudaStream_t s = g->stream;
+    const int k = g->k;
+    const M3Plan pl = m3_plan(k, pos_lo, pos_hi);
+    const uint32_t B3 = 1u << pl.b3, cells = 1u << (pl.b3 + pl.b2);
+    const uint64_t n_codes = 1ULL << (2 * k), n = pos_hi - pos_lo;
+    // a group never has more tiles / chunks than the whole range (+1 for its own alignment)
+    g->status.reserve((size_t)B3 * (pl.n_tiles + 1) * 4, s);                                          // H1T -> O1T
+    g->scratch1.reserve(std::max<size_t>((size_t)(pl.n_chunks + 1) * cells * 4, (n_codes + 1) * 4), s);   // H12 -> O2, later ranks
+    g->hist.reserve((size_t)(2 * cells + 2) * 4, s);                                                  // tot32 | base32
+    g->scratch0.reserve((n_codes + 1) * 4, s);                                                        // row starts of every code
     g->recA.reserve(std::max<size_t>(n * 8, n_codes * 4), s);
-    g->recB.reserve(n * 8, s);
-    g->g_pos.reserve(n * 4, s);
-    g->m3_tile_info.reserve((size_t)pl.n_tiles * 4, s);
-    uint32_t *tile_info = g->m3_tile_info.as<uint32_t>();
-    uint32_t *H1T = g->status.as<uint32_t>(), *H12 = g->scratch1.as<uint32_t>();
-    unsigned int *tot32 = g->hist.as<unsigned int>();
-    uint32_t *base32 = g->hist.as<uint32_t>() + cells;
-    uint32_t *rowtab = g->scratch0.as<uint32_t>();
-    PDG_CUDA(cudaMemsetAsync(tot32, 0, cells * 4, s));
-
+    g->recB.reserve(std::max<size_t>(n * 8, 16), s);
+    g->g_pos.reserve(std::max<size_t>(n * 4, 16), s);
+    g->m3_tile_info.reserve((size_t)(pl.n_tiles + 1) * 4, s);
+    g->m3_gbase.reserve((size_t)max_groups * (cells + 1) * 4 + (size_t)max_groups * 4, s);
+    g->m3_groups.clear();
+    g->m3_max_groups = max_groups;
+    g->m3_pos_lo = pos_lo;
     static bool attr_set = false;
     if (!attr_set) {
         PDG_CUDA(cudaFuncSetAttribute(m3_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 1 << 16));
@@ -367,13 +402,31 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
         PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
         attr_set = true;
     }
+}
+
+void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64_t pos1) {
+    cudaStream_t s = g->stream;
+    const int k = g->k;
+    if (g->m3_groups.size() >= g->m3_max_groups) {
+        set_error("msd3_stage_group: more than %u groups", g->m3_max_groups);
+        throw CudaError{PDG_E_INVALID};
+    }
+    const M3Plan pl = m3_plan(k, pos0, pos1);
+    const uint32_t B3 = 1u << pl.b3, cells = 1u << (pl.b3 + pl.b2);
+    const uint32_t gi = (uint32_t)g->m3_groups.size();
+    const uint64_t rec_off = pos0 - g->m3_pos_lo;     // a group has at most one record per position
+    uint32_t *tile_info = g->m3_tile_info.as<uint32_t>();
+    uint32_t *H1T = g->status.as<uint32_t>(), *H12 = g->scratch1.as<uint32_t>();
+    unsigned int *tot32 = g->hist.as<unsigned int>();
+    uint32_t *base32 = g->m3_gbase.as<uint32_t>() + (size_t)gi * (cells + 1);   // kept for pass 3
+    PDG_CUDA(cudaMemsetAsync(tot32, 0, cells * 4, s));
     const uint2 *packed = g->packed.as<uint2>();
     const uint64_t pw = g->packed.cap / 8;
     m3_tile_info_kernel<<<(pl.n_tiles + 255) / 256, 256, 0, s>>>(ct, pl, k, tile_info);
     PDG_LAUNCHED(g);
     // CUDA events around every launch of the sort (bench.py's roofline numbers): event i precedes
     // stage i of {hist, scans, pass 1, pass 2, pass 3}
-    const bool timed = g->collect_sort_stats;
+    const bool timed = g->collect_sort_stats && gi == 0;
     if (timed)
         while (g->k_events.size() < 6) {
             cudaEvent_t ev;
@@ -392,18 +445,46 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     m3_scan_tiles_kernel<<<pl.n_chunks, 256, 0, s>>>(H1T, pl, H12, base32);
     PDG_LAUNCHED(g);
     mark(2);
-    m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, ct, pl, tile_info, H1T, g->recA.as<uint64_t>());
+    m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, ct, pl, tile_info, H1T,
+                                                                     g->recA.as<uint64_t>() + rec_off);
     PDG_LAUNCHED(g);
     mark(3);
-    m3_pass2_kernel<7><<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem), s>>>(g->recA.as<uint2>(), pl, H1T, H12, base32,
-                                                                         g->recB.as<uint64_t>());
+    m3_pass2_kernel<7><<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem), s>>>(g->recA.as<uint2>() + rec_off, pl, H1T, H12, base32,
+                                                                         g->recB.as<uint64_t>() + rec_off);
     PDG_LAUNCHED(g);
     mark(4);
-    m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, base32, rowtab,
+    g->m3_groups.push_back(pdg_graph::M3Group{pos0, pos1, rec_off});
+}
+
+void msd3_finish(pdg_graph *g, uint64_t n) {
+    cudaStream_t s = g->stream;
+    const int k = g->k;
+    const M3Plan pl = m3_plan(k, 0, 32);   // digit widths only
+    const uint32_t cells = 1u << (pl.b3 + pl.b2);
+    const uint32_t G = (uint32_t)g->m3_groups.size();
+    const uint64_t n_codes = 1ULL << (2 * k);
+    uint32_t *gbase = g->m3_gbase.as<uint32_t>();
+    uint32_t *goff = gbase + (size_t)g->m3_max_groups * (cells + 1);
+    unsigned int *tot32 = g->hist.as<unsigned int>();
+    uint32_t *base32 = g->hist.as<uint32_t>() + cells;
+    uint32_t *rowtab = g->scratch0.as<uint32_t>();
+    std::vector<uint32_t> h_off(G);
+    for (uint32_t i = 0; i < G; ++i) h_off[i] = (uint32_t)g->m3_groups[i].rec_off;
+    PDG_CUDA(cudaMemcpyAsync(goff, h_off.data(), G * 4, cudaMemcpyHostToDevice, s));
+    if (G == 1) {
+        base32 = gbase;   // the group's bases are the global ones
+    } else {
+        m3_cell_totals_kernel<<<(cells + 255) / 256, 256, 0, s>>>(gbase, G, cells, tot32);
+        PDG_LAUNCHED(g);
+        m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32);
+        PDG_LAUNCHED(g);
+    }
+    const bool timed = g->collect_sort_stats && G == 1;
+    m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
                                                               g->g_pos.as<uint32_t>());
     PDG_LAUNCHED(g);
-    mark(5);
     if (timed) {
+        PDG_CUDA(cudaEventRecord(g->k_events[5], s));
         PDG_CUDA(cudaEventSynchronize(g->k_events[5]));
         float ms[5] = {0, 0, 0, 0, 0};
         for (int i = 0; i < 5; ++i) cudaEventElapsedTime(&ms[i], g->k_events[i], g->k_events[i + 1]);
@@ -417,6 +498,7 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     }
     g->stats.sort_passes = 3;
     g->stats.sort_records = n;
+    g->stats.sort_groups = G;
     // sentinel: rowtab[n_codes] = n
     const uint32_t n32 = (uint32_t)n;
     PDG_CUDA(cudaMemcpyAsync(rowtab + n_codes, &n32, 4, cudaMemcpyHostToDevice, s));
@@ -427,13 +509,20 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
     exclusive_scan_u32_u32(flags, rank, n_codes, g);
     uint32_t nn = 0;
     PDG_CUDA(cudaMemcpyAsync(&nn, rank + n_codes, 4, cudaMemcpyDeviceToHost, s));
-    PDG_CUDA(cudaStreamSynchronize(s));
+    PDG_CUDA(cudaStreamSynchronize(s));   // also covers h_off
     g->g_nodes = nn;
     g->g_codes.reserve(std::max<size_t>((size_t)nn * 8, 16), s);
     g->g_rowptr.reserve(((size_t)nn + 1) * 4, s);
     m3_compact_rows_kernel<<<grid_for(n_codes, 256), 256, 0, s>>>(rowtab, flags, rank, n_codes,
                                                                  g->g_codes.as<uint64_t>(), g->g_rowptr.as<uint32_t>());
     PDG_LAUNCHED(g);
+    g->m3_groups.clear();
+}
+
+void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
+    msd3_reserve(g, hc.pos0, hc.pos1, 1);
+    msd3_stage_group(g, ct, hc.pos0, hc.pos1);
+    msd3_finish(g, hc.n_kmers);
 }
 
 }  // namespace pdg
