@@ -263,7 +263,9 @@ def run_b200(a):
             "phases_ms": dict([(k, st[k]) for k in ("ms_upload", "ms_sort", "ms_explicit", "ms_nodes", "ms_total")] +
                               [("ms_ingest_a", st["ms_ingest_a"]), ("ms_ingest_b", st["ms_ingest_b"]),
                                ("ms_ingest_c", st["ms_ingest_c"]),
-                               ("e2e_ms_ingest_a_incl_h2d_wait", st_e2e["ms_ingest_a"])]),
+                               ("e2e_ms_ingest_call", st_e2e["ms_ingest_a"]), ("e2e_ms_h2d_copies", st_e2e["ms_ingest_b"]),
+                               ("e2e_ms_finalize", st_e2e["ms_total"]), ("e2e_pipelined", st_e2e["pipelined"]),
+                               ("e2e_sort_groups", st_e2e["sort_groups"])]),
         }
         if world == 1 and not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_reference(a, a.cpu_sample_bases)

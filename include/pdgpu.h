@@ -101,6 +101,7 @@ typedef struct pdg_build_stats {
      * includes waiting for the copies), pass B (scan), pass C (emit + header hashes) */
     float ms_ingest_a, ms_ingest_b, ms_ingest_c, pad3;
     uint64_t sort_groups;       /* groups of positions the k <= 11 index was staged in (1 unless pipelined) */
+    uint64_t pipelined;         /* 1 if passes 1-2 already ran inside pdg_ingest_fasta_batch (host images) */
     uint64_t ingest_bytes;      /* bytes parsed by the last pdg_ingest_fasta_batch */
     uint64_t ingest_launches;
 } pdg_build_stats;

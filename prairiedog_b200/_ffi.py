@@ -64,7 +64,7 @@ class BuildStats(ctypes.Structure):
                 ("ms_hist", ctypes.c_float), ("ms_scans", ctypes.c_float), ("ms_pass", ctypes.c_float * 3),
                 ("pad2", ctypes.c_float),
                 ("ms_ingest_a", ctypes.c_float), ("ms_ingest_b", ctypes.c_float), ("ms_ingest_c", ctypes.c_float),
-                ("pad3", ctypes.c_float), ("sort_groups", c_u64), ("ingest_bytes", c_u64), ("ingest_launches", c_u64)]
+                ("pad3", ctypes.c_float), ("sort_groups", c_u64), ("pipelined", c_u64), ("ingest_bytes", c_u64), ("ingest_launches", c_u64)]
 
 
 # name -> (restype, argtypes); every symbol of include/pdgpu.h (tests/test_abi.py checks the list

@@ -80,6 +80,10 @@ void pdg_destroy(pdg_graph *g) {
         cudaStreamSynchronize(g->copy_stream);
         cudaStreamDestroy(g->copy_stream);
     }
+    if (g->aux_stream) {
+        cudaStreamSynchronize(g->aux_stream);
+        cudaStreamDestroy(g->aux_stream);
+    }
     delete g;
 }
 
@@ -92,6 +96,7 @@ int pdg_set_stream(pdg_graph *g, void *cuda_stream) {
 
 int pdg_clear(pdg_graph *g) {
     PDG_API_BEGIN
+    g->pre_valid = false;   // scratch buffers of a pipelined ingest may be reused from here on
     PDG_CUDA(cudaStreamSynchronize(g->stream));
     g->n_res = 0;
     if (g->packed.p) PDG_CUDA(cudaMemsetAsync(g->packed.p, 0, g->packed.cap, g->stream));
@@ -112,6 +117,7 @@ int pdg_clear(pdg_graph *g) {
 int pdg_ingest_fasta(pdg_graph *g, const uint8_t *d_bytes, uint64_t n_bytes, uint64_t *h_header_table,
                      uint64_t cap_headers, pdg_ingest_info *info) {
     PDG_API_BEGIN
+    g->pre_valid = false;   // scratch buffers of a pipelined ingest may be reused from here on
     if (!info || (n_bytes && !d_bytes)) {
         set_error("pdg_ingest_fasta: null argument");
         return PDG_E_INVALID;
@@ -160,12 +166,14 @@ int pdg_add_contigs(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len
 int pdg_kmer_stats(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len, uint64_t n_contigs,
                    uint64_t *n_kmers, uint64_t *n_unique) {
     PDG_API_BEGIN
+    g->pre_valid = false;   // scratch buffers of a pipelined ingest may be reused from here on
     return kmer_stats(g, h_begin, h_len, n_contigs, n_kmers, n_unique);
     PDG_API_END
 }
 
 int pdg_emit_codes(pdg_graph *g, uint64_t begin, uint64_t len, uint64_t *d_codes_out) {
     PDG_API_BEGIN
+    g->pre_valid = false;   // scratch buffers of a pipelined ingest may be reused from here on
     return emit_codes(g, begin, len, d_codes_out);
     PDG_API_END
 }

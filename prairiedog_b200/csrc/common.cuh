@@ -157,6 +157,7 @@ struct pdg_graph {
     struct M3Group { uint64_t pos0, pos1, rec_off; };
     std::vector<M3Group> m3_groups;      // groups staged since msd3_reserve
     uint32_t m3_max_groups = 0;
+    bool m3_timed = false;
     uint64_t m3_pos_lo = 0;
     pdg::DevBuf recA, recB, scratch0, scratch1, scratch2, status, hist;
     pdg::DevBuf q_a, q_b, q_cnt, q_cnt_g, q_off, q_hits, small;
@@ -169,7 +170,11 @@ struct pdg_graph {
 
     // ---- batched ingest (ingest_batch.cu) ----
     pdg::DevBuf stage, fb_files, fb_summ, fb_prefix, fb_totals;
-    cudaStream_t copy_stream = nullptr;
+    cudaStream_t copy_stream = nullptr, aux_stream = nullptr;
+    // pipelined build: contig table assumed at ingest time (device + host copy), valid until anything else touches the graph
+    pdg::DevBuf pre_ct;
+    std::vector<uint64_t> pre_begin, pre_len;
+    bool pre_valid = false;
     cudaEvent_t fb_ev_ready = nullptr;
     std::vector<cudaEvent_t> fb_events, i_events;
     float ms_ingest[3] = {0, 0, 0};

@@ -22,8 +22,10 @@
 // by file, so results never depend on which path ran (tests/test_gpu_ingest_batch.py).
 // With PDG_IN_HOST the images are host buffers: they are copied to a device staging area on a
 // second stream in groups, and pass A of a group overlaps the copy of the next one.
-#include "common.cuh"
+#include "gindex.cuh"
+#include "msd3.cuh"
 #include <algorithm>
+#include <stdlib.h>
 
 namespace pdg {
 
@@ -195,13 +197,13 @@ __global__ void __launch_bounds__(FB_THREADS) fb_summ_kernel(const FbFile *__res
 }
 
 // ---- pass B: one CTA per file -------------------------------------------------------------------
-__global__ void __launch_bounds__(FB_THREADS) fb_scan_kernel(const FbFile *__restrict__ files,
+__global__ void __launch_bounds__(FB_THREADS) fb_scan_kernel(const FbFile *__restrict__ files, uint32_t f_begin,
                                                              const FbTileSumm *__restrict__ summ,
                                                              FbTilePrefix *__restrict__ prefix,
                                                              FbFileTotals *__restrict__ totals) {
     __shared__ uint32_t s_warp[FB_WARPS];
     __shared__ uint32_t s_imp;
-    const uint32_t f = blockIdx.x;
+    const uint32_t f = f_begin + blockIdx.x;
     const uint64_t t0 = files[f].tile0, nt = files[f + 1].tile0 - t0;
     uint64_t c_res = 0, c_hdr = 0;
     uint32_t c_state = 0;
@@ -248,12 +250,13 @@ __device__ __forceinline__ uint64_t fb_slice(uint64_t half, uint32_t s, uint32_t
 }
 
 __global__ void __launch_bounds__(FB_THREADS) fb_emit_kernel(const FbFile *__restrict__ files, uint32_t n_files,
+                                                             uint64_t tile_begin,
                                                              const FbTilePrefix *__restrict__ prefix,
                                                              unsigned long long *__restrict__ packed,
                                                              uint64_t *__restrict__ table) {
     __shared__ uint32_t s_warp[FB_WARPS];
     __shared__ unsigned long long words[FB_WORDS];
-    const uint64_t tile = blockIdx.x;
+    const uint64_t tile = tile_begin + blockIdx.x;
     const uint32_t f = fb_file_of(files, n_files, tile);
     const FbFile fi = files[f];
     const FbTilePrefix tp = prefix[tile];
@@ -327,17 +330,22 @@ __global__ void __launch_bounds__(FB_THREADS) fb_emit_kernel(const FbFile *__res
 
 // One thread per header row: closes a header ended by end of file and hashes the right-stripped
 // line (FNV-1a).  Hash 0 = "compare the bytes on the host" (line ends in a non-ASCII byte).
-__global__ void fb_hash_kernel(const FbFile *__restrict__ files, uint32_t n_files,
-                               const FbFileTotals *__restrict__ totals, uint64_t n_rows,
-                               uint64_t *__restrict__ table) {
-    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n_rows) return;
-    uint32_t lo = 0, hi = n_files;   // last file with hdr_base <= r that owns rows
+// last file of [f0, f1) whose hdr_base <= r (files without rows share the base of the next one)
+__device__ __forceinline__ uint32_t fb_file_of_row(const FbFile *__restrict__ files, uint32_t f0, uint32_t f1, uint64_t r) {
+    uint32_t lo = f0, hi = f1;
     while (lo < hi) {
         const uint32_t mid = (lo + hi) >> 1;
         if (files[mid].hdr_base <= r) lo = mid + 1; else hi = mid;
     }
-    const uint32_t f = lo - 1;
+    return lo - 1;
+}
+
+__global__ void fb_hash_kernel(const FbFile *__restrict__ files, uint32_t f0, uint32_t f1,
+                               const FbFileTotals *__restrict__ totals, uint64_t row_begin, uint64_t row_end,
+                               uint64_t *__restrict__ table) {
+    const uint64_t r = row_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= row_end) return;
+    const uint32_t f = fb_file_of_row(files, f0, f1, r);
     const FbFile fi = files[f];
     uint64_t *row = table + 4 * r;
     if (r + 1 == fi.hdr_base + totals[f].hdr && totals[f].state == 1u) row[1] = fi.n_bytes;
@@ -352,6 +360,23 @@ __global__ void fb_hash_kernel(const FbFile *__restrict__ files, uint32_t n_file
     if (h == 0) h = 1;
     if (e > b && fi.bytes[e - 1] >= 0x80) h = 0;
     row[3] = h;
+}
+
+// Header rows -> the contig table the reference's loader would build from a well-formed file
+// (kmers.py:61-75): row r covers residues [res_base + residue_index(r), start of the next row or
+// the end of the file).  Used by the pipelined build; the host checks later that the caller
+// declared exactly these contigs.
+__global__ void fb_contigs_kernel(const FbFile *__restrict__ files, uint32_t f0, uint32_t f1,
+                                  const FbFileTotals *__restrict__ totals, uint64_t row_begin, uint64_t row_end,
+                                  const uint64_t *__restrict__ table, uint64_t *__restrict__ ct_begin,
+                                  uint64_t *__restrict__ ct_end) {
+    const uint64_t r = row_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= row_end) return;
+    const uint32_t f = fb_file_of_row(files, f0, f1, r);
+    const FbFile fi = files[f];
+    const bool last = r + 1 == fi.hdr_base + totals[f].hdr;
+    ct_begin[r] = fi.res_base + table[4 * r + 2];
+    ct_end[r] = fi.res_base + (last ? totals[f].res : table[4 * (r + 1) + 2]);
 }
 
 // ---- host -----------------------------------------------------------------------------------------
@@ -372,6 +397,160 @@ static int batch_fallback(pdg_graph *g, const std::vector<const uint8_t *> &dev,
         }
         row += infos[f].n_headers;
     }
+    return PDG_OK;
+}
+
+// ---- pipelined build (host images, k <= 11, empty graph) -------------------------------------------
+// The copy of a 500 MB batch takes ~10 ms over PCIe 5 while parsing it takes < 1 ms, and the index
+// sort cannot finish before the last byte arrived.  So the batch is cut into copy groups and every
+// group is taken as far as it can go while the next ones are still in flight:
+//   copy stream : H2D group 0 | H2D group 1 | H2D group 2 | ...
+//   aux stream  :      pass A+B g0 | pass A+B g1 | ...                (needs only the group's bytes)
+//   main stream :        emit g0, contig table g0, hist + pass 1 + pass 2 g0 | emit g1, ...   (msd3_stage_group)
+// After the last group only pass 3 and the row table are left for pdg_finalize (msd3_finish).  The
+// library has to assume which contigs the caller will declare (pdg_add_contigs comes later): the ones
+// a well-formed file yields, one per header row.  pdg_finalize checks the declaration against that
+// assumption and falls back to the one-shot build when it differs.
+struct FbGroup { uint32_t f0, f1; uint64_t tb, te; };
+
+static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t *n_bytes, uint32_t n_files,
+                            uint64_t *h_table, uint64_t cap_headers, pdg_ingest_info *infos, std::vector<FbFile> &hf,
+                            const std::vector<const uint8_t *> &dev, uint64_t tiles, uint64_t group_bytes) {
+    cudaStream_t s = g->stream;
+    const int k = g->k;
+    // ---- groups ----
+    std::vector<FbGroup> groups;
+    uint64_t total_bytes = 0;
+    for (uint32_t f0 = 0; f0 < n_files;) {
+        uint32_t f1 = f0;
+        uint64_t bytes = 0;
+        while (f1 < n_files && (f1 == f0 || bytes + n_bytes[f1] <= group_bytes)) bytes += n_bytes[f1++];
+        groups.push_back(FbGroup{f0, f1, hf[f0].tile0, hf[f1].tile0});
+        total_bytes += bytes;
+        f0 = f1;
+    }
+    const uint32_t G = (uint32_t)groups.size();
+    // ---- every buffer up front (a reallocation in the middle would stall the pipeline) ----
+    const uint64_t words = (total_bytes + 31) / 32 + 2;          // residues <= bytes
+    g->packed.reserve(words * 8, s, /*keep=*/false, /*zero=*/true);
+    g->small.reserve((cap_headers * 4 + 8) * sizeof(uint64_t), s);
+    g->pre_ct.reserve((2 * cap_headers + 4) * sizeof(uint64_t), s);
+    msd3_reserve(g, 0, std::max<uint64_t>(total_bytes, 32), G);
+    if (!g->aux_stream) PDG_CUDA(cudaStreamCreateWithFlags(&g->aux_stream, cudaStreamNonBlocking));
+    while (g->fb_events.size() < 2 * (size_t)G + 1) {
+        cudaEvent_t ev;
+        PDG_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        g->fb_events.push_back(ev);
+    }
+    FbFile *d_files = g->fb_files.as<FbFile>();
+    FbTileSumm *d_summ = g->fb_summ.as<FbTileSumm>();
+    FbTilePrefix *d_prefix = g->fb_prefix.as<FbTilePrefix>();
+    FbFileTotals *d_tot = g->fb_totals.as<FbFileTotals>();
+    uint64_t *d_table = g->small.as<uint64_t>();
+    uint64_t *ct_begin = g->pre_ct.as<uint64_t>(), *ct_end = ct_begin + cap_headers + 2;
+    // everything queued on s so far (file table upload, reserves, staging area readers) precedes the copies
+    cudaEvent_t ev_ready = g->fb_events[2 * G];
+    PDG_CUDA(cudaEventRecord(ev_ready, s));
+    PDG_CUDA(cudaStreamWaitEvent(g->copy_stream, ev_ready, 0));
+    PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, ev_ready, 0));
+    for (uint32_t gi = 0; gi < G; ++gi) {
+        for (uint32_t f = groups[gi].f0; f < groups[gi].f1; ++f)
+            if (n_bytes[f])
+                PDG_CUDA(cudaMemcpyAsync(const_cast<uint8_t *>(dev[f]), ptrs[f], n_bytes[f], cudaMemcpyHostToDevice,
+                                         g->copy_stream));
+        PDG_CUDA(cudaEventRecord(g->fb_events[2 * gi], g->copy_stream));
+    }
+    PDG_CUDA(cudaEventRecord(g->i_events[2], g->copy_stream));   // last byte on the device
+    std::vector<FbFileTotals> tot(n_files);
+    uint64_t n_rows = 0, n_res = 0;
+    bool pure = true, fits = true;
+    for (uint32_t gi = 0; gi < G; ++gi) {
+        const FbGroup &gr = groups[gi];
+        const uint32_t nf = gr.f1 - gr.f0;
+        // pass A + B of the group as soon as its bytes are on the device
+        PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, g->fb_events[2 * gi], 0));
+        if (gr.te > gr.tb) {
+            fb_summ_kernel<<<(unsigned)(gr.te - gr.tb), FB_THREADS, 0, g->aux_stream>>>(d_files, n_files, gr.tb, d_summ);
+            PDG_LAUNCHED(g);
+        }
+        fb_scan_kernel<<<nf, FB_THREADS, 0, g->aux_stream>>>(d_files, gr.f0, d_summ, d_prefix, d_tot);
+        PDG_LAUNCHED(g);
+        PDG_CUDA(cudaMemcpyAsync(tot.data() + gr.f0, d_tot + gr.f0, nf * sizeof(FbFileTotals), cudaMemcpyDeviceToHost,
+                                 g->aux_stream));
+        PDG_CUDA(cudaEventRecord(g->fb_events[2 * gi + 1], g->aux_stream));
+        PDG_CUDA(cudaEventSynchronize(g->fb_events[2 * gi + 1]));
+        const uint64_t row_begin = n_rows, res_begin = n_res;
+        for (uint32_t f = gr.f0; f < gr.f1; ++f) {
+            pdg_ingest_info o{};
+            o.n_bytes = n_bytes[f];
+            o.n_headers = tot[f].hdr;
+            o.n_residues = tot[f].res;
+            o.residue_base = g->n_res + n_res;
+            o.appended = 1;
+            infos[f] = o;
+            hf[f].res_base = g->n_res + n_res;
+            hf[f].hdr_base = n_rows;
+            n_rows += tot[f].hdr;
+            n_res += tot[f].res;
+            pure = pure && tot[f].impure == 0;
+        }
+        fits = fits && n_rows <= cap_headers;
+        if (!pure || !fits) continue;   // keep collecting the totals of every file, stage nothing more
+        PDG_CUDA(cudaMemcpyAsync(d_files + gr.f0, hf.data() + gr.f0, nf * sizeof(FbFile), cudaMemcpyHostToDevice, s));
+        if (gr.te > gr.tb) {
+            fb_emit_kernel<<<(unsigned)(gr.te - gr.tb), FB_THREADS, 0, s>>>(d_files, n_files, gr.tb, d_prefix,
+                                                                           g->packed.as<unsigned long long>(), d_table);
+            PDG_LAUNCHED(g);
+        }
+        const uint64_t rows = n_rows - row_begin;
+        if (rows) {
+            const unsigned grid = (unsigned)((rows + 127) / 128);
+            fb_hash_kernel<<<grid, 128, 0, s>>>(d_files, gr.f0, gr.f1, d_tot, row_begin, n_rows, d_table);
+            PDG_LAUNCHED(g);
+            fb_contigs_kernel<<<grid, 128, 0, s>>>(d_files, gr.f0, gr.f1, d_tot, row_begin, n_rows, d_table, ct_begin, ct_end);
+            PDG_LAUNCHED(g);
+        }
+        if (n_res > res_begin && rows) {
+            ContigTable ct{};
+            ct.begin = ct_begin + row_begin;
+            ct.end = ct_end + row_begin;
+            ct.kbase = nullptr;
+            ct.type = nullptr;
+            ct.n = rows;
+            msd3_stage_group(g, ct, g->n_res + res_begin, g->n_res + n_res);
+        }
+    }
+    hf[n_files].hdr_base = n_rows;
+    if (!fits || !pure) {
+        // nothing may stay behind: the store beyond n_res has to be zero for the next append
+        PDG_CUDA(cudaStreamSynchronize(g->aux_stream));
+        PDG_CUDA(cudaMemsetAsync(g->packed.p, 0, g->packed.cap, s));
+        g->m3_groups.clear();
+        if (!fits) {
+            set_error("pdg_ingest_fasta_batch: %llu headers, table capacity %llu", (unsigned long long)n_rows,
+                      (unsigned long long)cap_headers);
+            PDG_CUDA(cudaStreamSynchronize(s));
+            return PDG_E_CAPACITY;
+        }
+        return batch_fallback(g, dev, n_bytes, n_files, h_table, infos);
+    }
+    if (n_rows)
+        PDG_CUDA(cudaMemcpyAsync(h_table, d_table, n_rows * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    // the contigs this build assumed (host copy, checked by pdg_finalize)
+    g->pre_begin.clear();
+    g->pre_len.clear();
+    for (uint32_t f = 0; f < n_files; ++f)
+        for (uint64_t r = hf[f].hdr_base; r < hf[f].hdr_base + tot[f].hdr; ++r) {
+            const uint64_t b = hf[f].res_base + h_table[4 * r + 2];
+            const uint64_t e = hf[f].res_base + (r + 1 == hf[f].hdr_base + tot[f].hdr ? tot[f].res : h_table[4 * (r + 1) + 2]);
+            if (e - b > (uint64_t)k) {
+                g->pre_begin.push_back(b);
+                g->pre_len.push_back(e - b);
+            }
+        }
+    g->pre_valid = !g->m3_groups.empty();
+    g->n_res += n_res;
     return PDG_OK;
 }
 
@@ -425,6 +604,24 @@ int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t 
     }
     const uint64_t launches0 = g->launches;
     PDG_CUDA(cudaEventRecord(g->i_events[0], s));
+    static const uint64_t group_bytes =
+        getenv("PDG_FB_GROUP_BYTES") ? (uint64_t)atoll(getenv("PDG_FB_GROUP_BYTES")) : FB_GROUP_BYTES;
+    static const bool no_pipeline = getenv("PDG_NO_PIPELINE") != nullptr;
+    g->pre_valid = false;
+    if (host_src && !no_pipeline && 2 * g->k <= kMsd3MaxBits && g->n_res == 0 && g->c_begin.empty() &&
+        g->x_src.empty() && g->x_nodes.empty() && tiles) {
+        const int rc = ingest_pipelined(g, ptrs, n_bytes, n_files, h_table, cap_headers, infos, hf, dev, tiles, group_bytes);
+        PDG_CUDA(cudaEventRecord(g->i_events[1], s));
+        PDG_CUDA(cudaEventSynchronize(g->i_events[1]));
+        cudaEventElapsedTime(&g->ms_ingest[0], g->i_events[0], g->i_events[1]);   // whole call
+        g->ms_ingest[1] = g->ms_ingest[2] = 0.f;
+        if (rc == PDG_OK && g->pre_valid) cudaEventElapsedTime(&g->ms_ingest[1], g->i_events[0], g->i_events[2]);   // copies only
+        uint64_t nb = 0;
+        for (uint32_t f = 0; f < n_files; ++f) nb += n_bytes[f];
+        g->ingest_bytes = nb;
+        g->ingest_launches = g->launches - launches0;
+        return rc;
+    }
     // ---- pass A (host mode: per copy group, overlapping the next group's copy) ----
     if (host_src) {
         // the staging area may still be read by work queued on s; order the copies after it
@@ -436,7 +633,7 @@ int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t 
         while (f0 < n_files) {
             uint32_t f1 = f0;
             uint64_t bytes = 0;
-            while (f1 < n_files && (f1 == f0 || bytes + n_bytes[f1] <= FB_GROUP_BYTES)) {
+            while (f1 < n_files && (f1 == f0 || bytes + n_bytes[f1] <= group_bytes)) {
                 if (n_bytes[f1])
                     PDG_CUDA(cudaMemcpyAsync(const_cast<uint8_t *>(dev[f1]), ptrs[f1], n_bytes[f1],
                                              cudaMemcpyHostToDevice, g->copy_stream));
@@ -463,7 +660,7 @@ int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t 
         PDG_LAUNCHED(g);
     }
     PDG_CUDA(cudaEventRecord(g->i_events[1], s));
-    fb_scan_kernel<<<n_files, FB_THREADS, 0, s>>>(d_files, d_summ, d_prefix, d_tot);
+    fb_scan_kernel<<<n_files, FB_THREADS, 0, s>>>(d_files, 0, d_summ, d_prefix, d_tot);
     PDG_LAUNCHED(g);
     PDG_CUDA(cudaEventRecord(g->i_events[2], s));
     std::vector<FbFileTotals> tot(n_files);
@@ -501,12 +698,12 @@ int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t 
     PDG_CUDA(cudaMemcpyAsync(d_files, hf.data(), (n_files + 1) * sizeof(FbFile), cudaMemcpyHostToDevice, s));
     PDG_CUDA(cudaEventRecord(g->i_events[3], s));
     if (tiles) {
-        fb_emit_kernel<<<(unsigned)tiles, FB_THREADS, 0, s>>>(d_files, n_files, d_prefix,
+        fb_emit_kernel<<<(unsigned)tiles, FB_THREADS, 0, s>>>(d_files, n_files, 0, d_prefix,
                                                              g->packed.as<unsigned long long>(), d_table);
         PDG_LAUNCHED(g);
     }
     if (n_rows) {
-        fb_hash_kernel<<<(unsigned)((n_rows + 127) / 128), 128, 0, s>>>(d_files, n_files, d_tot, n_rows, d_table);
+        fb_hash_kernel<<<(unsigned)((n_rows + 127) / 128), 128, 0, s>>>(d_files, 0, n_files, d_tot, 0, n_rows, d_table);
         PDG_LAUNCHED(g);
     }
     PDG_CUDA(cudaEventRecord(g->i_events[4], s));

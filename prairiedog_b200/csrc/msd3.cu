@@ -371,6 +371,10 @@ static M3Plan m3_plan(int k, uint64_t pos0, uint64_t pos1) {
     // ranges of pass 2 average ~m3_range records (a few tiles each: little padding, still >> SMs ranges)
     static const uint32_t m3_range = getenv("PDG_M3_RANGE") ? (uint32_t)atoi(getenv("PDG_M3_RANGE")) : 6000u;
     pl.ch = std::max<uint32_t>(1, (uint32_t)(((uint64_t)m3_range << pl.b3) / M3_TILE));
+    // a small range of positions (one group of a pipelined ingest) still has to fill the GPU: the histogram
+    // kernel runs one CTA per chunk
+    static const uint32_t m3_min_chunks = getenv("PDG_M3_MIN_CHUNKS") ? (uint32_t)atoi(getenv("PDG_M3_MIN_CHUNKS")) : 148u;
+    pl.ch = std::max<uint32_t>(1, std::min<uint32_t>(pl.ch, (pl.n_tiles + m3_min_chunks - 1) / m3_min_chunks));
     pl.n_chunks = (pl.n_tiles + pl.ch - 1) / pl.ch;
     return pl;
 }
@@ -453,6 +457,7 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
                                                                          g->recB.as<uint64_t>() + rec_off);
     PDG_LAUNCHED(g);
     mark(4);
+    g->m3_timed = timed;
     g->m3_groups.push_back(pdg_graph::M3Group{pos0, pos1, rec_off});
 }
 
@@ -479,7 +484,7 @@ void msd3_finish(pdg_graph *g, uint64_t n) {
         m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32);
         PDG_LAUNCHED(g);
     }
-    const bool timed = g->collect_sort_stats && G == 1;
+    const bool timed = g->collect_sort_stats && G == 1 && g->m3_timed;   // passes 1-2 were timed in this call
     m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
                                                               g->g_pos.as<uint32_t>());
     PDG_LAUNCHED(g);

@@ -32,7 +32,7 @@ def test_struct_layouts(lib_built):
     from prairiedog_b200.engine import HIT_DTYPE
     assert ctypes.sizeof(_ffi.Hit) == 16 == HIT_DTYPE.itemsize
     assert ctypes.sizeof(_ffi.IngestInfo) == 48
-    assert ctypes.sizeof(_ffi.BuildStats) == 192
+    assert ctypes.sizeof(_ffi.BuildStats) == 200
     import numpy as np
     assert np.dtype(_ffi.INGEST_INFO_DTYPE).itemsize == 48
     lib = _ffi.load()

@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import golden, data_path, DATA
+from conftest import golden, data_path, DATA, ROOT
 
 pytestmark = pytest.mark.gpu
 
@@ -191,3 +191,76 @@ def test_duplicate_headers_in_batch_keep_set_semantics():
     g3.save()
     assert g2.canonical() == g3.canonical()
     assert g1.canonical()[0] != []
+
+
+def _pipelined_worker(group_bytes, k, n_genomes, n_bases, n_contigs, out):
+    """runs in a fresh process: the group size of the pipelined build is read once from the environment"""
+    import os
+    import sys
+    os.environ["PDG_FB_GROUP_BYTES"] = str(group_bytes)
+    sys.path.insert(0, ROOT)
+    import numpy as np
+    from prairiedog_b200 import B200Graph, synth
+    from oracle.c_oracle import COracle
+    files = [(name, buf, None) for name, buf, _ in synth.genomes(n_genomes, n_bases=n_bases, n_contigs=n_contigs)]
+    g = B200Graph(k=k)
+    counts = g.add_fasta_batch(files)
+    g.save()
+    st = g.engine.stats()
+    o = COracle(k)
+    for _, buf, _ in files:
+        o.add_fasta_bytes(buf)
+    o.build()
+    ok = g.engine.counts() == o.counts() and g.engine.checksum() == o.checksum()
+    for got, want in zip(g.engine.export_index(), o.index()):
+        ok = ok and bool(np.array_equal(got, want))
+    # a second save without changes rebuilds in one shot and must give the same graph
+    g._unsaved = True
+    g.save()
+    ok2 = g.engine.checksum() == o.checksum()
+    with open(out, "w") as f:
+        f.write("%d %d %d %d %d" % (ok, ok2, st["pipelined"], st["sort_groups"], sum(counts)))
+
+
+@pytest.mark.parametrize("group_bytes,k", [(60_000, 11), (250_000, 11), (60_000, 7), (1 << 25, 11), (100_000, 4)])
+def test_pipelined_build_equals_oracle(tmp_path, group_bytes, k):
+    """host images, k <= 11, empty graph: passes 1-2 run per copy group inside the ingest call, pass 3 in
+    pdg_finalize; small groups force many groups (and groups smaller than a tile)"""
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "r.txt")
+    ctx = mp.get_context("spawn")
+    p = ctx.Process(target=_pipelined_worker, args=(group_bytes, k, 6, 120_000, 9, out))
+    p.start()
+    p.join(600)
+    assert p.exitcode == 0
+    ok, ok2, pipelined, groups, n = map(int, open(out).read().split())
+    assert ok == 1 and ok2 == 1 and pipelined == 1
+    assert groups == (6 if group_bytes < 130_000 else 1 if group_bytes > 1_000_000 else groups) and 1 <= groups <= 6
+    assert group_bytes > 1_000_000 or groups >= 3
+
+
+def test_pipelined_build_falls_back_when_contigs_differ():
+    """the ingest assumed one contig per header; the caller declares something else -> one-shot build"""
+    from prairiedog_b200.engine import Engine
+    from oracle.c_oracle import COracle
+    import torch
+    imgs = _synthetic(3, 100_000, 5)
+    e = Engine(11)
+    pinned = [torch.from_numpy(i.copy()).pin_memory() for i in imgs]
+    infos, table, row_base = e.ingest_batch([p.data_ptr() for p in pinned], [i.size for i in imgs], host=True)
+    # declare only the contigs of the first two files
+    nh = int(row_base[2])
+    res = table[:nh, 2].astype(np.int64)
+    fo = np.repeat(np.arange(2), np.diff(row_base[:3]))
+    begin = res + infos["residue_base"].astype(np.int64)[fo]
+    end = np.empty_like(res)
+    end[:-1] = res[1:]
+    end[row_base[1:3] - 1] = infos["n_residues"].astype(np.int64)[:2]
+    e.add_contigs(begin, end - res, np.arange(nh, dtype=np.uint32))
+    e.finalize()
+    assert e.stats()["pipelined"] == 0
+    o = COracle(11)
+    for i in imgs[:2]:
+        o.add_fasta_bytes(i)
+    o.build()
+    assert e.counts() == o.counts() and e.checksum() == o.checksum()
