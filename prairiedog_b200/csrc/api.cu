@@ -97,6 +97,8 @@ int pdg_set_stream(pdg_graph *g, void *cuda_stream) {
 int pdg_clear(pdg_graph *g) {
     PDG_API_BEGIN
     g->pre_valid = false;   // scratch buffers of a pipelined ingest may be reused from here on
+    g->m3_groups.clear();
+    g->m3_launched = false;
     PDG_CUDA(cudaStreamSynchronize(g->stream));
     g->n_res = 0;
     if (g->packed.p) PDG_CUDA(cudaMemsetAsync(g->packed.p, 0, g->packed.cap, g->stream));

@@ -116,6 +116,7 @@ void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, i
     g->collect_sort_stats = false;
     g->pre_valid = false;
     g->m3_groups.clear();
+    g->m3_launched = false;
     g->stats.sort_passes = passes;
     g->stats.sort_records = n;
     // O(1) lookup for small k: presence bitmap + popcount prefix (rank == row id)

@@ -47,7 +47,9 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc);
 // the same build in steps (groups of positions staged one by one, ingest_batch.cu)
 void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_groups);
 void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64_t pos1);
-void msd3_finish(pdg_graph *g, uint64_t n_kmers);
+void msd3_finish_launch(pdg_graph *g);                 // pass 3 + presence + ranks, asynchronous
+void msd3_finish_complete(pdg_graph *g, uint64_t n_kmers);
+void msd3_finish(pdg_graph *g, uint64_t n_kmers);      // launch (unless already launched) + complete
 
 // xbuild.cu: builds the explicit part from g->x_* plus the demoted contigs
 void build_x_part(pdg_graph *g, const HostContigs &demoted);

@@ -534,9 +534,15 @@ static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint
         }
         return batch_fallback(g, dev, n_bytes, n_files, h_table, infos);
     }
+    // the header table goes back on the aux stream so that the main stream can carry on with pass 3
+    // (speculatively: pdg_finalize redoes the build if the caller declares other contigs) while the
+    // caller does its bookkeeping
+    PDG_CUDA(cudaEventRecord(g->i_events[1], s));                 // end of the ingest proper
+    PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, g->i_events[1], 0));
     if (n_rows)
-        PDG_CUDA(cudaMemcpyAsync(h_table, d_table, n_rows * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
-    PDG_CUDA(cudaStreamSynchronize(s));
+        PDG_CUDA(cudaMemcpyAsync(h_table, d_table, n_rows * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, g->aux_stream));
+    if (!g->m3_groups.empty()) msd3_finish_launch(g);
+    PDG_CUDA(cudaStreamSynchronize(g->aux_stream));
     // the contigs this build assumed (host copy, checked by pdg_finalize)
     g->pre_begin.clear();
     g->pre_len.clear();
@@ -611,8 +617,10 @@ int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t 
     if (host_src && !no_pipeline && 2 * g->k <= kMsd3MaxBits && g->n_res == 0 && g->c_begin.empty() &&
         g->x_src.empty() && g->x_nodes.empty() && tiles) {
         const int rc = ingest_pipelined(g, ptrs, n_bytes, n_files, h_table, cap_headers, infos, hf, dev, tiles, group_bytes);
-        PDG_CUDA(cudaEventRecord(g->i_events[1], s));
-        PDG_CUDA(cudaEventSynchronize(g->i_events[1]));
+        if (!(rc == PDG_OK && g->pre_valid)) {   // else: recorded before pass 3 was launched, and complete
+            PDG_CUDA(cudaEventRecord(g->i_events[1], s));
+            PDG_CUDA(cudaEventSynchronize(g->i_events[1]));
+        }
         cudaEventElapsedTime(&g->ms_ingest[0], g->i_events[0], g->i_events[1]);   // whole call
         g->ms_ingest[1] = g->ms_ingest[2] = 0.f;
         if (rc == PDG_OK && g->pre_valid) cudaEventElapsedTime(&g->ms_ingest[1], g->i_events[0], g->i_events[2]);   // copies only

@@ -104,7 +104,9 @@ __global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const uint2 *__res
 
 // base32[cell] = exclusive scan of tot32 (cells + 1 entries; the last is n).  One CTA.
 __global__ void __launch_bounds__(1024) m3_base_kernel(const unsigned int *__restrict__ tot32, uint32_t cells,
-                                                       uint32_t *__restrict__ base32) {
+                                                       uint32_t *__restrict__ base32, uint32_t *__restrict__ note,
+                                                       uint32_t note_value) {
+    if (note && threadIdx.x == 0) *note = note_value;   // a group's record offset, for pass 3
     uint64_t carry = 0;
     for (uint32_t b = 0; b < cells; b += 1024) {
         const uint32_t i = b + threadIdx.x;
@@ -396,6 +398,7 @@ void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_g
     g->m3_tile_info.reserve((size_t)(pl.n_tiles + 1) * 4, s);
     g->m3_gbase.reserve((size_t)max_groups * (cells + 1) * 4 + (size_t)max_groups * 4, s);
     g->m3_groups.clear();
+    g->m3_launched = false;
     g->m3_max_groups = max_groups;
     g->m3_pos_lo = pos_lo;
     static bool attr_set = false;
@@ -442,7 +445,8 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
     m3_hist_kernel<<<pl.n_chunks, M3H_THREADS, cells * 4, s>>>(packed, pw, k, ct, pl, tile_info, H1T, H12, tot32);
     PDG_LAUNCHED(g);
     mark(1);
-    m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32);
+    uint32_t *goff = g->m3_gbase.as<uint32_t>() + (size_t)g->m3_max_groups * (cells + 1);
+    m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32, goff + gi, (uint32_t)rec_off);
     PDG_LAUNCHED(g);
     m3_scan_chunks_kernel<<<(cells + 255) / 256, 256, 0, s>>>(H12, pl.n_chunks, cells, base32);
     PDG_LAUNCHED(g);
@@ -461,7 +465,10 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
     g->m3_groups.push_back(pdg_graph::M3Group{pos0, pos1, rec_off});
 }
 
-void msd3_finish(pdg_graph *g, uint64_t n) {
+// Pass 3 + presence + ranks, all asynchronous on the graph's stream: a pipelined ingest launches
+// this speculatively when its last group is staged, so that it runs while the caller declares
+// the contigs.  msd3_finish_complete reads the node count back and writes the rows.
+void msd3_finish_launch(pdg_graph *g) {
     cudaStream_t s = g->stream;
     const int k = g->k;
     const M3Plan pl = m3_plan(k, 0, 32);   // digit widths only
@@ -469,28 +476,44 @@ void msd3_finish(pdg_graph *g, uint64_t n) {
     const uint32_t G = (uint32_t)g->m3_groups.size();
     const uint64_t n_codes = 1ULL << (2 * k);
     uint32_t *gbase = g->m3_gbase.as<uint32_t>();
-    uint32_t *goff = gbase + (size_t)g->m3_max_groups * (cells + 1);
+    uint32_t *goff = gbase + (size_t)g->m3_max_groups * (cells + 1);   // written by every group's m3_base_kernel
     unsigned int *tot32 = g->hist.as<unsigned int>();
     uint32_t *base32 = g->hist.as<uint32_t>() + cells;
     uint32_t *rowtab = g->scratch0.as<uint32_t>();
-    std::vector<uint32_t> h_off(G);
-    for (uint32_t i = 0; i < G; ++i) h_off[i] = (uint32_t)g->m3_groups[i].rec_off;
-    PDG_CUDA(cudaMemcpyAsync(goff, h_off.data(), G * 4, cudaMemcpyHostToDevice, s));
     if (G == 1) {
         base32 = gbase;   // the group's bases are the global ones
     } else {
         m3_cell_totals_kernel<<<(cells + 255) / 256, 256, 0, s>>>(gbase, G, cells, tot32);
         PDG_LAUNCHED(g);
-        m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32);
+        m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32, nullptr, 0u);
         PDG_LAUNCHED(g);
     }
-    const bool timed = g->collect_sort_stats && G == 1 && g->m3_timed;   // passes 1-2 were timed in this call
     m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
                                                               g->g_pos.as<uint32_t>());
     PDG_LAUNCHED(g);
-    if (timed) {
+    if (g->collect_sort_stats && G == 1 && g->m3_timed)   // passes 1-2 were timed in this call
         PDG_CUDA(cudaEventRecord(g->k_events[5], s));
-        PDG_CUDA(cudaEventSynchronize(g->k_events[5]));
+    // sentinel: rowtab[n_codes] = number of records (= base of the cell past the last)
+    PDG_CUDA(cudaMemcpyAsync(rowtab + n_codes, base32 + cells, 4, cudaMemcpyDeviceToDevice, s));
+    // rows: presence -> rank
+    uint32_t *flags = g->recA.as<uint32_t>(), *rank = g->scratch1.as<uint32_t>();
+    m3_present_kernel<<<grid_for(n_codes, 256), 256, 0, s>>>(rowtab, n_codes, flags);
+    PDG_LAUNCHED(g);
+    exclusive_scan_u32_u32(flags, rank, n_codes, g);
+    g->m3_launched = true;
+}
+
+void msd3_finish_complete(pdg_graph *g, uint64_t n) {
+    cudaStream_t s = g->stream;
+    const int k = g->k;
+    const uint32_t G = (uint32_t)g->m3_groups.size();
+    const uint64_t n_codes = 1ULL << (2 * k);
+    uint32_t *rowtab = g->scratch0.as<uint32_t>();
+    uint32_t *flags = g->recA.as<uint32_t>(), *rank = g->scratch1.as<uint32_t>();
+    uint32_t nn = 0;
+    PDG_CUDA(cudaMemcpyAsync(&nn, rank + n_codes, 4, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    if (g->collect_sort_stats && G == 1 && g->m3_timed) {
         float ms[5] = {0, 0, 0, 0, 0};
         for (int i = 0; i < 5; ++i) cudaEventElapsedTime(&ms[i], g->k_events[i], g->k_events[i + 1]);
         g->stats.ms_hist = ms[0];
@@ -504,17 +527,6 @@ void msd3_finish(pdg_graph *g, uint64_t n) {
     g->stats.sort_passes = 3;
     g->stats.sort_records = n;
     g->stats.sort_groups = G;
-    // sentinel: rowtab[n_codes] = n
-    const uint32_t n32 = (uint32_t)n;
-    PDG_CUDA(cudaMemcpyAsync(rowtab + n_codes, &n32, 4, cudaMemcpyHostToDevice, s));
-    // rows: presence -> rank -> (codes, rowptr)
-    uint32_t *flags = g->recA.as<uint32_t>(), *rank = g->scratch1.as<uint32_t>();
-    m3_present_kernel<<<grid_for(n_codes, 256), 256, 0, s>>>(rowtab, n_codes, flags);
-    PDG_LAUNCHED(g);
-    exclusive_scan_u32_u32(flags, rank, n_codes, g);
-    uint32_t nn = 0;
-    PDG_CUDA(cudaMemcpyAsync(&nn, rank + n_codes, 4, cudaMemcpyDeviceToHost, s));
-    PDG_CUDA(cudaStreamSynchronize(s));   // also covers h_off
     g->g_nodes = nn;
     g->g_codes.reserve(std::max<size_t>((size_t)nn * 8, 16), s);
     g->g_rowptr.reserve(((size_t)nn + 1) * 4, s);
@@ -522,6 +534,12 @@ void msd3_finish(pdg_graph *g, uint64_t n) {
                                                                  g->g_codes.as<uint64_t>(), g->g_rowptr.as<uint32_t>());
     PDG_LAUNCHED(g);
     g->m3_groups.clear();
+    g->m3_launched = false;
+}
+
+void msd3_finish(pdg_graph *g, uint64_t n) {
+    if (!g->m3_launched) msd3_finish_launch(g);
+    msd3_finish_complete(g, n);
 }
 
 void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc) {
