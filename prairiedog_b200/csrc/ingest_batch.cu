@@ -415,12 +415,14 @@ struct FbGroup { uint32_t f0, f1; uint64_t tb, te; };
 
 static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t *n_bytes, uint32_t n_files,
                             uint64_t *h_table, uint64_t cap_headers, pdg_ingest_info *infos, std::vector<FbFile> &hf,
-                            const std::vector<const uint8_t *> &dev, uint64_t tiles, uint64_t group_bytes) {
+                            const std::vector<const uint8_t *> &dev, uint64_t tiles, uint64_t group_bytes, bool host_src) {
     cudaStream_t s = g->stream;
     const int k = g->k;
     // ---- groups ----
     std::vector<FbGroup> groups;
     uint64_t total_bytes = 0;
+    // (groups that taper off towards the end were tried: the fixed cost of a group -- a host round trip
+    // for the totals and ~12 launches -- outweighs the shorter tail; 16.1 vs 15.1 ms per config-3 step)
     for (uint32_t f0 = 0; f0 < n_files;) {
         uint32_t f1 = f0;
         uint64_t bytes = 0;
@@ -451,16 +453,19 @@ static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint
     // everything queued on s so far (file table upload, reserves, staging area readers) precedes the copies
     cudaEvent_t ev_ready = g->fb_events[2 * G];
     PDG_CUDA(cudaEventRecord(ev_ready, s));
-    PDG_CUDA(cudaStreamWaitEvent(g->copy_stream, ev_ready, 0));
     PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, ev_ready, 0));
-    for (uint32_t gi = 0; gi < G; ++gi) {
-        for (uint32_t f = groups[gi].f0; f < groups[gi].f1; ++f)
-            if (n_bytes[f])
-                PDG_CUDA(cudaMemcpyAsync(const_cast<uint8_t *>(dev[f]), ptrs[f], n_bytes[f], cudaMemcpyHostToDevice,
-                                         g->copy_stream));
-        PDG_CUDA(cudaEventRecord(g->fb_events[2 * gi], g->copy_stream));
+    if (host_src) {
+        PDG_CUDA(cudaStreamWaitEvent(g->copy_stream, ev_ready, 0));
+        for (uint32_t gi = 0; gi < G; ++gi) {
+            for (uint32_t f = groups[gi].f0; f < groups[gi].f1; ++f)
+                if (n_bytes[f])
+                    PDG_CUDA(cudaMemcpyAsync(const_cast<uint8_t *>(dev[f]), ptrs[f], n_bytes[f], cudaMemcpyHostToDevice,
+                                             g->copy_stream));
+            PDG_CUDA(cudaEventRecord(g->fb_events[2 * gi], g->copy_stream));
+        }
+        PDG_CUDA(cudaEventRecord(g->i_events[2], g->copy_stream));   // last byte on the device
     }
-    PDG_CUDA(cudaEventRecord(g->i_events[2], g->copy_stream));   // last byte on the device
+    const bool time_kernels = !host_src && G == 1;   // device images: one group, its launches run alone
     std::vector<FbFileTotals> tot(n_files);
     uint64_t n_rows = 0, n_res = 0;
     bool pure = true, fits = true;
@@ -468,11 +473,13 @@ static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint
         const FbGroup &gr = groups[gi];
         const uint32_t nf = gr.f1 - gr.f0;
         // pass A + B of the group as soon as its bytes are on the device
-        PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, g->fb_events[2 * gi], 0));
+        if (host_src) PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, g->fb_events[2 * gi], 0));
+        if (time_kernels) PDG_CUDA(cudaEventRecord(g->i_events[6], g->aux_stream));
         if (gr.te > gr.tb) {
             fb_summ_kernel<<<(unsigned)(gr.te - gr.tb), FB_THREADS, 0, g->aux_stream>>>(d_files, n_files, gr.tb, d_summ);
             PDG_LAUNCHED(g);
         }
+        if (time_kernels) PDG_CUDA(cudaEventRecord(g->i_events[7], g->aux_stream));
         fb_scan_kernel<<<nf, FB_THREADS, 0, g->aux_stream>>>(d_files, gr.f0, d_summ, d_prefix, d_tot);
         PDG_LAUNCHED(g);
         PDG_CUDA(cudaMemcpyAsync(tot.data() + gr.f0, d_tot + gr.f0, nf * sizeof(FbFileTotals), cudaMemcpyDeviceToHost,
@@ -497,11 +504,13 @@ static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint
         fits = fits && n_rows <= cap_headers;
         if (!pure || !fits) continue;   // keep collecting the totals of every file, stage nothing more
         PDG_CUDA(cudaMemcpyAsync(d_files + gr.f0, hf.data() + gr.f0, nf * sizeof(FbFile), cudaMemcpyHostToDevice, s));
+        if (time_kernels) PDG_CUDA(cudaEventRecord(g->i_events[3], s));
         if (gr.te > gr.tb) {
             fb_emit_kernel<<<(unsigned)(gr.te - gr.tb), FB_THREADS, 0, s>>>(d_files, n_files, gr.tb, d_prefix,
                                                                            g->packed.as<unsigned long long>(), d_table);
             PDG_LAUNCHED(g);
         }
+        if (time_kernels) PDG_CUDA(cudaEventRecord(g->i_events[4], s));
         const uint64_t rows = n_rows - row_begin;
         if (rows) {
             const unsigned grid = (unsigned)((rows + 127) / 128);
@@ -537,8 +546,8 @@ static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint
     // the header table goes back on the aux stream so that the main stream can carry on with pass 3
     // (speculatively: pdg_finalize redoes the build if the caller declares other contigs) while the
     // caller does its bookkeeping
-    PDG_CUDA(cudaEventRecord(g->i_events[1], s));                 // end of the ingest proper
-    PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, g->i_events[1], 0));
+    PDG_CUDA(cudaEventRecord(g->i_events[5], s));                 // end of the ingest proper
+    PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, g->i_events[5], 0));
     if (n_rows)
         PDG_CUDA(cudaMemcpyAsync(h_table, d_table, n_rows * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, g->aux_stream));
     if (!g->m3_groups.empty()) msd3_finish_launch(g);
@@ -603,7 +612,7 @@ int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t 
     FbTilePrefix *d_prefix = g->fb_prefix.as<FbTilePrefix>();
     FbFileTotals *d_tot = g->fb_totals.as<FbFileTotals>();
     PDG_CUDA(cudaMemcpyAsync(d_files, hf.data(), (n_files + 1) * sizeof(FbFile), cudaMemcpyHostToDevice, s));
-    while (g->i_events.size() < 5) {
+    while (g->i_events.size() < 8) {
         cudaEvent_t ev;
         PDG_CUDA(cudaEventCreate(&ev));
         g->i_events.push_back(ev);
@@ -614,16 +623,24 @@ int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t 
         getenv("PDG_FB_GROUP_BYTES") ? (uint64_t)atoll(getenv("PDG_FB_GROUP_BYTES")) : FB_GROUP_BYTES;
     static const bool no_pipeline = getenv("PDG_NO_PIPELINE") != nullptr;
     g->pre_valid = false;
-    if (host_src && !no_pipeline && 2 * g->k <= kMsd3MaxBits && g->n_res == 0 && g->c_begin.empty() &&
+    if (!no_pipeline && 2 * g->k <= kMsd3MaxBits && g->n_res == 0 && g->c_begin.empty() &&
         g->x_src.empty() && g->x_nodes.empty() && tiles) {
-        const int rc = ingest_pipelined(g, ptrs, n_bytes, n_files, h_table, cap_headers, infos, hf, dev, tiles, group_bytes);
-        if (!(rc == PDG_OK && g->pre_valid)) {   // else: recorded before pass 3 was launched, and complete
-            PDG_CUDA(cudaEventRecord(g->i_events[1], s));
-            PDG_CUDA(cudaEventSynchronize(g->i_events[1]));
+        // device images are one group: nothing to overlap but the caller's own bookkeeping
+        const int rc = ingest_pipelined(g, ptrs, n_bytes, n_files, h_table, cap_headers, infos, hf, dev, tiles,
+                                        host_src ? group_bytes : ~0ULL, host_src);
+        const bool launched = rc == PDG_OK && g->pre_valid;
+        if (!launched) {   // else: i_events[5] was recorded before pass 3 was launched, and is complete
+            PDG_CUDA(cudaEventRecord(g->i_events[5], s));
+            PDG_CUDA(cudaEventSynchronize(g->i_events[5]));
         }
-        cudaEventElapsedTime(&g->ms_ingest[0], g->i_events[0], g->i_events[1]);   // whole call
-        g->ms_ingest[1] = g->ms_ingest[2] = 0.f;
-        if (rc == PDG_OK && g->pre_valid) cudaEventElapsedTime(&g->ms_ingest[1], g->i_events[0], g->i_events[2]);   // copies only
+        g->ms_ingest[0] = g->ms_ingest[1] = g->ms_ingest[2] = 0.f;
+        if (host_src) {
+            cudaEventElapsedTime(&g->ms_ingest[0], g->i_events[0], g->i_events[5]);   // whole call
+            if (launched) cudaEventElapsedTime(&g->ms_ingest[1], g->i_events[0], g->i_events[2]);   // copies only
+        } else if (launched) {
+            cudaEventElapsedTime(&g->ms_ingest[0], g->i_events[6], g->i_events[7]);   // pass A
+            cudaEventElapsedTime(&g->ms_ingest[2], g->i_events[3], g->i_events[4]);   // pass C
+        }
         uint64_t nb = 0;
         for (uint32_t f = 0; f < n_files; ++f) nb += n_bytes[f];
         g->ingest_bytes = nb;

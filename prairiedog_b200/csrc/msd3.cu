@@ -267,6 +267,9 @@ __global__ void m3_cell_totals_kernel(const uint32_t *__restrict__ gbase, uint32
     tot[c] = t;
 }
 
+#ifndef M3_COUNT_UNROLL
+#define M3_COUNT_UNROLL 4
+#endif
 template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ gbase,
@@ -287,7 +290,15 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uin
     for (uint32_t gi = 0; gi < n_groups; ++gi) {
         const uint32_t *gb = gbase + (size_t)gi * cells1;
         const uint32_t sb = goff[gi] + gb[cell], se = goff[gi] + gb[cell + 1];
-        for (uint32_t i = sb + tid; i < se; i += M3_THREADS) atomicAdd(&sm.delta[in[i].y & m1], 1u);
+        // four loads in flight per thread: the bucket is read cold here (and again, from L2, below)
+        for (uint32_t i = sb + tid; i < se; i += M3_COUNT_UNROLL * M3_THREADS) {
+            uint32_t cd[M3_COUNT_UNROLL];
+#pragma unroll
+            for (int u = 0; u < M3_COUNT_UNROLL; ++u) cd[u] = i + u * M3_THREADS < se ? in[i + u * M3_THREADS].y : 0xffffffffu;
+#pragma unroll
+            for (int u = 0; u < M3_COUNT_UNROLL; ++u)
+                if (cd[u] != 0xffffffffu) atomicAdd(&sm.delta[cd[u] & m1], 1u);
+        }
     }
     __syncthreads();
     {   // exclusive scan of the 256 counts -> first occurrence of every code of the bucket
@@ -433,7 +444,7 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
     PDG_LAUNCHED(g);
     // CUDA events around every launch of the sort (bench.py's roofline numbers): event i precedes
     // stage i of {hist, scans, pass 1, pass 2, pass 3}
-    const bool timed = g->collect_sort_stats && gi == 0;
+    const bool timed = gi == 0 && g->m3_max_groups == 1;   // a single group's launches run back to back on s
     if (timed)
         while (g->k_events.size() < 6) {
             cudaEvent_t ev;
@@ -491,7 +502,7 @@ void msd3_finish_launch(pdg_graph *g) {
     m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
                                                               g->g_pos.as<uint32_t>());
     PDG_LAUNCHED(g);
-    if (g->collect_sort_stats && G == 1 && g->m3_timed)   // passes 1-2 were timed in this call
+    if (G == 1 && g->m3_timed)   // the group's other stages were timed
         PDG_CUDA(cudaEventRecord(g->k_events[5], s));
     // sentinel: rowtab[n_codes] = number of records (= base of the cell past the last)
     PDG_CUDA(cudaMemcpyAsync(rowtab + n_codes, base32 + cells, 4, cudaMemcpyDeviceToDevice, s));
@@ -513,7 +524,7 @@ void msd3_finish_complete(pdg_graph *g, uint64_t n) {
     uint32_t nn = 0;
     PDG_CUDA(cudaMemcpyAsync(&nn, rank + n_codes, 4, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
-    if (g->collect_sort_stats && G == 1 && g->m3_timed) {
+    if (G == 1 && g->m3_timed) {
         float ms[5] = {0, 0, 0, 0, 0};
         for (int i = 0; i < 5; ++i) cudaEventElapsedTime(&ms[i], g->k_events[i], g->k_events[i + 1]);
         g->stats.ms_hist = ms[0];
