@@ -113,13 +113,57 @@ def run_reference(a):
 
 # ------------------------------------------------------------------ clocks
 class ClockSampler(object):
+    """SM clock and throttle reasons DURING the timed region.  NVML in a thread (a sample costs
+    microseconds; the timed region of the default run is ~50 ms, shorter than one `nvidia-smi` start-up),
+    `nvidia-smi -lms` only if the NVML binding is missing."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
         self.rows, self.p, self.index = [], None, index
+        self.nvml, self.h, self.stop_flag, self.sm, self.reasons, self.mx = None, None, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML counts physical devices; honour CUDA_VISIBLE_DEVICES
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                ids = [x.strip() for x in vis.split(",") if x.strip()]
+                if index < len(ids) and ids[index].isdigit():
+                    phys = int(ids[index])
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def sample(self):
+        n = self.nvml
+        try:
+            self.sm.append(float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)))
+            r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for name, bit in (("hw_slowdown", n.nvmlClocksThrottleReasonHwSlowdown),
+                              ("hw_thermal_slowdown", n.nvmlClocksThrottleReasonHwThermalSlowdown),
+                              ("sw_thermal_slowdown", n.nvmlClocksThrottleReasonSwThermalSlowdown),
+                              ("sw_power_cap", n.nvmlClocksThrottleReasonSwPowerCap)):
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def _loop(self):
+        while not self.stop_flag:
+            self.sample()
+            time.sleep(0.002)
 
     def start(self):
+        if self.nvml:
+            self.stop_flag = False
+            self.t = threading.Thread(target=self._loop, daemon=True)
+            self.t.start()
+            return
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                        "--format=csv,noheader,nounits", "-lms", "100"],
@@ -134,12 +178,18 @@ class ClockSampler(object):
             self.rows.append(ln.strip())
 
     def stop(self):
+        if self.nvml:
+            self.sample()            # at least one sample, taken before the last step has drained
+            self.stop_flag = True
+            self.t.join(timeout=2)
+            sm = sorted(self.sm)
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.mx, "reasons": sorted(self.reasons),
+                    "samples": len(sm), "source": "nvml"}
         if not self.p:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.p.terminate()
         self.t.join(timeout=2)
         sm, mx, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 7:
@@ -149,12 +199,12 @@ class ClockSampler(object):
                 mx = float(f[1])
             except ValueError:
                 continue
-            for n, v in zip(names, f[3:7]):
+            for n, v in zip(self.NAMES, f[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvidia-smi"}
 
 
 # ------------------------------------------------------------------ B200 arm
@@ -209,8 +259,8 @@ def run_b200(a):
         for _ in range(steps):
             out = step(resident)
         e1.record()
+        clocks = sampler.stop() if sampler else None        # last sample while the last step is still running
         torch.cuda.synchronize()
-        clocks = sampler.stop() if sampler else None
         if world > 1:
             dist.barrier()
         ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)

@@ -48,7 +48,7 @@
 extern "C" {
 #endif
 
-#define PDG_ABI_VERSION 3
+#define PDG_ABI_VERSION 4
 
 #define PDG_OK            0
 #define PDG_E_INVALID    -1   /* bad argument / bad state */
@@ -159,6 +159,22 @@ int pdg_kmer_stats(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len,
  * a bulk call.  pdg_fetch_residues decodes the same range back to ASCII (host output). */
 int pdg_emit_codes(pdg_graph *g, uint64_t begin, uint64_t len, uint64_t *d_codes_out);
 int pdg_fetch_residues(pdg_graph *g, uint64_t begin, uint64_t len, uint8_t *h_ascii);
+
+/* Persistent snapshot.  Replaces the LMDB file LGGraph.save copies around
+ * (lemon_graph.py:154-157, Snakefile:99-100): what is saved is the INPUT of pdg_finalize -- the
+ * 2-bit store (0.25 B/bp), the declared contigs and the explicit edges / nodes -- because rebuilding
+ * the index from it (tens of Gbp/s) is faster than reading an index back from disk.
+ * pdg_snapshot_sizes: out = {n_residues, n_contigs, n_explicit_edges, n_explicit_nodes}.
+ * pdg_snapshot_export copies them to host arrays of at least those sizes (h_words: at least
+ * (n_residues + 31) / 32 words; residue i is bits 63-2*(i%32) .. of word i/32, A=0 T=1 C=2 G=3).
+ * pdg_store_import replaces the store of an EMPTY graph (after pdg_create / pdg_clear); contigs,
+ * edges and nodes are then declared with pdg_add_contigs / pdg_add_edges_host / pdg_add_nodes_host. */
+int pdg_snapshot_sizes(pdg_graph *g, uint64_t *out4);
+int pdg_snapshot_export(pdg_graph *g, uint64_t *h_words, uint64_t cap_words, uint64_t *h_begin,
+                        uint64_t *h_len, uint32_t *h_type_id, uint64_t *h_src_code,
+                        uint64_t *h_tgt_code, uint32_t *h_edge_type_id, int32_t *h_value,
+                        uint64_t *h_node_code);
+int pdg_store_import(pdg_graph *g, const uint64_t *h_words, uint64_t n_residues);
 
 /* Per-edge compatibility path: LGGraph.add_edge / upsert_node (lemon_graph.py:99-128) and
  * graph_edge_resolve / graph_node_resolve (cffi_stubs.py).  Host arrays are copied. */

@@ -83,6 +83,9 @@ SIGNATURES = {
     "pdg_kmer_stats": (c_int, [vp, vp, vp, c_u64, u64p, u64p]),
     "pdg_emit_codes": (c_int, [vp, c_u64, c_u64, vp]),
     "pdg_fetch_residues": (c_int, [vp, c_u64, c_u64, vp]),
+    "pdg_snapshot_sizes": (c_int, [vp, vp]),
+    "pdg_snapshot_export": (c_int, [vp, vp, c_u64, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "pdg_store_import": (c_int, [vp, vp, c_u64]),
     "pdg_add_edges_host": (c_int, [vp, vp, vp, vp, vp, c_u64]),
     "pdg_add_nodes_host": (c_int, [vp, vp, c_u64]),
     "pdg_finalize": (c_int, [vp, c_int]),
@@ -121,8 +124,8 @@ def load(build_if_missing=False):
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    if lib.pdg_abi_version() != 3:
-        raise PdgError(PDG_E_INVALID, "libpdgpu ABI %d, expected 3: rebuild" % lib.pdg_abi_version())
+    if lib.pdg_abi_version() != 4:
+        raise PdgError(PDG_E_INVALID, "libpdgpu ABI %d, expected 4: rebuild" % lib.pdg_abi_version())
     _lib = lib
     return lib
 

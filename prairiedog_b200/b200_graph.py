@@ -171,11 +171,29 @@ class B200Graph(Graph):
             self._st_nodes = []
 
     def save(self, f: str = None):
-        """lemon_graph.py:154-157: commit.  Everything added so far becomes visible to queries."""
+        """lemon_graph.py:154-157: commit.  Everything added so far becomes visible to queries.
+        Like LGGraph.save the file name is ignored (SubgraphRef passes its .rdf name to every
+        backend, subgraph_ref.py:117-125); snapshot(f) writes the graph to disk."""
         self._flush()
         self.engine.finalize()
         self._unsaved = False
         self._published = True
+
+    def snapshot(self, f: str) -> str:
+        """Publishes and writes the graph to ``f`` (the role of the LMDB file the Snakefile copies to
+        outputs/pangenome_*.g, Snakefile:99-100); B200Graph.load reads it back."""
+        from . import snapshot
+        self._publish()
+        return snapshot.save(self, f)
+
+    @classmethod
+    def load(cls, f: str, device: int = 0, path_limit: int = None) -> "B200Graph":
+        """A graph from a file written by snapshot(f): the genome store and the contig table go back to
+        the GPU and the index is rebuilt there."""
+        from . import snapshot
+        meta, _ = snapshot.read(f)
+        g = cls(k=meta["k"], device=device, path_limit=path_limit)
+        return snapshot.load(g, f)
 
     def _publish(self):
         if self._unsaved:
@@ -431,6 +449,25 @@ class B200Graph(Graph):
             return a, np.zeros(len(pairs) + 1, dtype=np.uint64), np.zeros(0, dtype=HIT_DTYPE)
         off, hits = self.engine.query_paths(a, b, self.path_limit if limit is None else limit)
         return a, off, hits
+
+    def query_many(self, pairs, limit=None, strings=True):
+        """Prairiedog.query (prairiedog.py:17-33) for a batch of (src, dst) pairs: per pair the list of
+        hit dicts {'string', 'edge_type', 'i', 'j'}; 'string' is concat_values (node.py:22-37) of the
+        hit's node chain, spelled from the codes without building Node objects."""
+        a, off, hits = self.path_many(pairs, limit)
+        out = []
+        for q in range(len(pairs)):
+            row = []
+            for h in hits[int(off[q]):int(off[q + 1])]:
+                d = {'edge_type': self._type_string(h["type_id"]), 'i': int(h["i"]), 'j': int(h["j"])}
+                if strings:
+                    codes, status = self.engine.walk(int(a[q]), h)
+                    assert status == 0, "Length of chains is {} != 1".format(0 if status == 1 else 2)
+                    vals = [self._value(c) for c in codes.tolist()]
+                    d['string'] = vals[0] + ''.join(v[-1] for v in vals[1:])
+                row.append(d)
+            out.append(row)
+        return out
 
     def path(self, node_a: str, node_b: str) -> typing.Tuple[tuple, tuple]:
         """lemon_graph.py:275-334."""

@@ -3,6 +3,7 @@
 #include <stdarg.h>
 #include <string.h>
 #include <new>
+#include <algorithm>
 
 namespace pdg {
 static thread_local char g_err[1024] = "";
@@ -183,6 +184,70 @@ int pdg_emit_codes(pdg_graph *g, uint64_t begin, uint64_t len, uint64_t *d_codes
 int pdg_fetch_residues(pdg_graph *g, uint64_t begin, uint64_t len, uint8_t *h_ascii) {
     PDG_API_BEGIN
     return fetch_residues(g, begin, len, h_ascii);
+    PDG_API_END
+}
+
+int pdg_snapshot_sizes(pdg_graph *g, uint64_t *out4) {
+    PDG_API_BEGIN
+    out4[0] = g->n_res;
+    out4[1] = g->c_begin.size();
+    out4[2] = g->x_src.size();
+    out4[3] = g->x_nodes.size();
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_snapshot_export(pdg_graph *g, uint64_t *h_words, uint64_t cap_words, uint64_t *h_begin, uint64_t *h_len,
+                        uint32_t *h_type_id, uint64_t *h_src_code, uint64_t *h_tgt_code, uint32_t *h_edge_type_id,
+                        int32_t *h_value, uint64_t *h_node_code) {
+    PDG_API_BEGIN
+    const uint64_t words = (g->n_res + 31) / 32;
+    if (words > cap_words) {
+        set_error("pdg_snapshot_export: %llu words, capacity %llu", (unsigned long long)words,
+                  (unsigned long long)cap_words);
+        return PDG_E_CAPACITY;
+    }
+    if (words) {
+        PDG_CUDA(cudaMemcpyAsync(h_words, g->packed.p, words * 8, cudaMemcpyDeviceToHost, g->stream));
+        PDG_CUDA(cudaStreamSynchronize(g->stream));
+    }
+    std::copy(g->c_begin.begin(), g->c_begin.end(), h_begin);
+    std::copy(g->c_len.begin(), g->c_len.end(), h_len);
+    std::copy(g->c_type.begin(), g->c_type.end(), h_type_id);
+    std::copy(g->x_src.begin(), g->x_src.end(), h_src_code);
+    std::copy(g->x_tgt.begin(), g->x_tgt.end(), h_tgt_code);
+    std::copy(g->x_type.begin(), g->x_type.end(), h_edge_type_id);
+    std::copy(g->x_val.begin(), g->x_val.end(), h_value);
+    std::copy(g->x_nodes.begin(), g->x_nodes.end(), h_node_code);
+    return PDG_OK;
+    PDG_API_END
+}
+
+int pdg_store_import(pdg_graph *g, const uint64_t *h_words, uint64_t n_residues) {
+    PDG_API_BEGIN
+    if (g->n_res || !g->c_begin.empty()) {
+        set_error("pdg_store_import: the graph already holds %llu residues (pdg_clear first)",
+                  (unsigned long long)g->n_res);
+        return PDG_E_INVALID;
+    }
+    g->pre_valid = false;
+    const uint64_t words = (n_residues + 31) / 32;
+    g->packed.reserve((words + 2) * 8, g->stream, /*keep=*/false, /*zero=*/true);
+    PDG_CUDA(cudaMemsetAsync(g->packed.p, 0, g->packed.cap, g->stream));
+    if (words) {
+        PDG_CUDA(cudaMemcpyAsync(g->packed.p, h_words, words * 8, cudaMemcpyHostToDevice, g->stream));
+        // the tail of the last word must be zero: later appends OR into it
+        const uint32_t used = (uint32_t)(n_residues & 31);
+        if (used) {
+            const uint64_t last = h_words[words - 1] & ~((1ULL << (64 - 2 * used)) - 1ULL);
+            PDG_CUDA(cudaStreamSynchronize(g->stream));
+            PDG_CUDA(cudaMemcpyAsync(g->packed.as<uint64_t>() + words - 1, &last, 8, cudaMemcpyHostToDevice, g->stream));
+        }
+        PDG_CUDA(cudaStreamSynchronize(g->stream));
+    }
+    g->n_res = n_residues;
+    g->finalized = false;
+    return PDG_OK;
     PDG_API_END
 }
 

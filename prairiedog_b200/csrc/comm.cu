@@ -5,11 +5,13 @@
 // edges of its own genomes (an edge is unique on (type,value) and a type belongs to one genome,
 // so edges never need to move), and only k-mer NODE keys are exchanged:
 //   1. each rank deduplicates its own k-mer codes                         (bitmap / sort+RLE)
-//   2. codes are hash partitioned, owner(code) = mix64(code) % world, and exchanged with ONE
+//   2. codes are range partitioned (range_owner below: equal slices of the key space) and exchanged with ONE
 //      grouped ncclSend/ncclRecv all-to-all (counts first, W x W uint64 ncclAllGather)
 //   3. each owner radix-sorts + run-length compacts what it received   -> its owned unique set
-//   4. the owned sets (disjoint) are all-gathered and sorted -> the same global node table,
-//      hence the same dense node ids, on every rank.
+//   4. the owned sets (disjoint ranges, ascending with the rank) are all-gathered in rank order -> the
+//      same sorted global node table, hence the same dense node ids, on every rank.
+// (Round 1 partitioned by hash: the gathered table then needed a full 64-bit sort on every rank,
+//  103 ms of a 160 ms step at k = 31 on 8 GPUs.)
 // NCCL is resolved with dlopen("libnccl.so.2") so that the library has no link-time dependency
 // on it and picks up the copy torch already loaded.
 #include "common.cuh"
@@ -74,25 +76,28 @@ struct CommError { int code; };
         }                                                                                     \
     } while (0)
 
-__global__ void owner_count_kernel(const uint64_t *__restrict__ codes, uint64_t n, uint32_t world,
-                                   unsigned long long *__restrict__ counts) {
-    __shared__ unsigned int sh[64];
-    if (threadIdx.x < 64) sh[threadIdx.x] = 0;
-    __syncthreads();
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) atomicAdd(&sh[mix64(codes[i]) % world], 1u);
-    __syncthreads();
-    if (threadIdx.x < world && sh[threadIdx.x]) atomicAdd(&counts[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
+// Owner of a node key: the key space is cut into `world` equal ranges (opaque keys, bit 63 set, sort
+// after every k-mer code and belong to the last rank).  Monotone in the key, so the owned sets are
+// disjoint RANGES: a rank's sorted table is already grouped by owner, and the owned sets of ranks
+// 0..W-1, concatenated, are the global sorted table -- no scatter before and no sort after the exchange.
+// code_bits = 2k.  Host mirror: prairiedog_b200/distributed.py:owner.
+__host__ __device__ __forceinline__ uint32_t range_owner(uint64_t key, int code_bits, uint32_t world) {
+    if (key >> 63) return world - 1;
+    const uint32_t t = code_bits >= 16 ? (uint32_t)(key >> (code_bits - 16)) : (uint32_t)(key << (16 - code_bits));
+    return (uint32_t)(((uint64_t)(t > 0xffffu ? 0xffffu : t) * world) >> 16);
 }
 
-__global__ void owner_scatter_kernel(const uint64_t *__restrict__ codes, uint64_t n, uint32_t world,
-                                     unsigned long long *__restrict__ cursors, uint64_t *__restrict__ out) {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint64_t c = codes[i];
-    // order inside a bucket is irrelevant: the owner sorts what it receives
-    const unsigned long long slot = atomicAdd(&cursors[mix64(c) % world], 1ULL);
-    out[slot] = c;
+// off[p] = first index of the sorted table whose owner is >= p (p = 0..world)
+__global__ void owner_bounds_kernel(const uint64_t *__restrict__ codes, uint64_t n, int code_bits, uint32_t world,
+                                    unsigned long long *__restrict__ off) {
+    const uint32_t p = threadIdx.x;
+    if (p > world) return;
+    uint64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        if (range_owner(codes[mid], code_bits, world) < p) lo = mid + 1; else hi = mid;
+    }
+    off[p] = p == world ? n : lo;
 }
 
 __global__ void head_flags_keys_kernel(const uint64_t *__restrict__ keys, uint64_t n, uint32_t *__restrict__ flags) {
@@ -191,30 +196,21 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
         if (use_bitmap) return comm_global_nodes_bitmap(g, api, n_global);
     }
 
-    // 1. bucket the local unique codes by owner
-    DevBuf &d_counts = g->c_counts, &d_all_counts = g->c_all_counts, &d_send = g->c_send, &d_recv = g->c_recv;
-    d_counts.reserve(2 * W * 8, s);
+    // 1. the local table is sorted, so the keys of owner p are the slice [send_off[p], send_off[p+1])
+    DevBuf &d_counts = g->c_counts, &d_all_counts = g->c_all_counts, &d_recv = g->c_recv;
+    d_counts.reserve((2 * W + 2) * 8, s);
     d_all_counts.reserve((size_t)W * W * 8, s);
-    PDG_CUDA(cudaMemsetAsync(d_counts.p, 0, 2 * W * 8, s));
-    unsigned long long *counts = d_counts.as<unsigned long long>();
-    unsigned long long *cursors = counts + W;
-    if (n_loc) {
-        owner_count_kernel<<<gridf(n_loc), 256, 0, s>>>(d_local, n_loc, W, counts);
-        PDG_LAUNCHED(g);
-    }
-    std::vector<uint64_t> h_send(W), h_all((size_t)W * W);
-    PDG_CUDA(cudaMemcpyAsync(h_send.data(), counts, W * 8, cudaMemcpyDeviceToHost, s));
+    unsigned long long *bounds = d_counts.as<unsigned long long>();      // W + 1 offsets
+    unsigned long long *counts = bounds + W + 1;                         // W counts
+    const int code_bits = 2 * g->k;
+    owner_bounds_kernel<<<1, 128, 0, s>>>(d_local, n_loc, code_bits, W, bounds);
+    PDG_LAUNCHED(g);
+    std::vector<uint64_t> send_off(W + 1), h_send(W), h_all((size_t)W * W);
+    PDG_CUDA(cudaMemcpyAsync(send_off.data(), bounds, (W + 1) * 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
-    std::vector<uint64_t> send_off(W + 1, 0);
-    for (int p = 0; p < W; ++p) send_off[p + 1] = send_off[p] + h_send[p];
-    PDG_CUDA(cudaMemcpyAsync(cursors, send_off.data(), W * 8, cudaMemcpyHostToDevice, s));
-    d_send.reserve(std::max<size_t>(n_loc * 8, 16), s);
-    if (n_loc) {
-        owner_scatter_kernel<<<gridf(n_loc), 256, 0, s>>>(d_local, n_loc, W, cursors,
-                                                         d_send.as<uint64_t>());
-        PDG_LAUNCHED(g);
-    }
-    // 2. counts matrix, then ONE grouped all-to-all of the codes
+    for (int p = 0; p < W; ++p) h_send[p] = send_off[p + 1] - send_off[p];
+    PDG_CUDA(cudaMemcpyAsync(counts, h_send.data(), W * 8, cudaMemcpyHostToDevice, s));
+    // 2. counts matrix, then ONE grouped all-to-all of the codes, straight out of the local table
     PDG_NCCL(api, api->AllGather(counts, d_all_counts.p, W, ncclUint64, comm, s));
     PDG_CUDA(cudaMemcpyAsync(h_all.data(), d_all_counts.p, (size_t)W * W * 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
@@ -224,13 +220,13 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
     d_recv.reserve(std::max<size_t>(n_recv * 8, 16), s);
     PDG_NCCL(api, api->GroupStart());
     for (int p = 0; p < W; ++p) {
-        if (h_send[p]) PDG_NCCL(api, api->Send(d_send.as<uint64_t>() + send_off[p], h_send[p], ncclUint64, p, comm, s));
+        if (h_send[p]) PDG_NCCL(api, api->Send(d_local + send_off[p], h_send[p], ncclUint64, p, comm, s));
         const uint64_t rc = h_all[(size_t)p * W + R];
         if (rc) PDG_NCCL(api, api->Recv(d_recv.as<uint64_t>() + recv_off[p], rc, ncclUint64, p, comm, s));
     }
     PDG_NCCL(api, api->GroupEnd());
 
-    // 3. owner: sort + run-length compaction of what was received
+    // 3. owner: sort + run-length compaction of what was received (W sorted runs of one key range)
     uint64_t n_own = 0;
     DevBuf &d_own = g->c_own, &d_tmp = g->c_tmp;
     d_own.reserve(std::max<size_t>(n_recv * 8, 16), s);
@@ -249,31 +245,23 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
                                                          g->scratch1.as<uint64_t>(), n_recv, d_own.as<uint64_t>());
         PDG_LAUNCHED(g);
     }
-    // 4. all-gather the owned sets (they are disjoint) and sort once more
+    // 4. all-gather the owned sets in rank order: ranges ascend with the rank, so this IS the sorted
+    //    global table
     PDG_CUDA(cudaMemcpyAsync(counts, &n_own, 8, cudaMemcpyHostToDevice, s));
     PDG_NCCL(api, api->AllGather(counts, d_all_counts.p, 1, ncclUint64, comm, s));
     std::vector<uint64_t> own_counts(W);
     PDG_CUDA(cudaMemcpyAsync(own_counts.data(), d_all_counts.p, W * 8, cudaMemcpyDeviceToHost, s));
-    PDG_CUDA(cudaStreamSynchronize(s));
+    PDG_CUDA(cudaStreamSynchronize(s));   // the sends are done: d_local (which may live in u_codes_buf) is no longer read
     std::vector<uint64_t> own_off(W + 1, 0);
     for (int p = 0; p < W; ++p) own_off[p + 1] = own_off[p] + own_counts[p];
     const uint64_t n_glob = own_off[W];
-    DevBuf &d_all = g->c_all, &d_all2 = g->c_all2;
-    d_all.reserve(std::max<size_t>(n_glob * 8, 16), s);
-    d_all2.reserve(std::max<size_t>(n_glob * 8, 16), s);
+    g->u_codes_buf.reserve(std::max<size_t>(n_glob * 8, 16), s);
     PDG_NCCL(api, api->GroupStart());
     for (int p = 0; p < W; ++p)
         if (own_counts[p])
-            PDG_NCCL(api, api->Broadcast(d_own.p, d_all.as<uint64_t>() + own_off[p], own_counts[p], ncclUint64, p, comm, s));
+            PDG_NCCL(api, api->Broadcast(d_own.p, g->u_codes_buf.as<uint64_t>() + own_off[p], own_counts[p], ncclUint64, p,
+                                         comm, s));
     PDG_NCCL(api, api->GroupEnd());
-    uint64_t *glob = d_all.as<uint64_t>();
-    if (n_glob > 1) {
-        uint64_t pr = 0;
-        glob = radix_sort_keys(g, d_all.as<uint64_t>(), d_all2.as<uint64_t>(), n_glob, 0, key_bits, &pr);
-    }
-    PDG_CUDA(cudaStreamSynchronize(s));   // d_local (which may live in u_codes_buf) is no longer read
-    g->u_codes_buf.reserve(std::max<size_t>(n_glob * 8, 16), s);
-    if (n_glob) PDG_CUDA(cudaMemcpyAsync(g->u_codes_buf.p, glob, n_glob * 8, cudaMemcpyDeviceToDevice, s));
     PDG_CUDA(cudaStreamSynchronize(s));
     *n_global = n_glob;
     return PDG_OK;

@@ -6,8 +6,8 @@ conventions the CUDA side (csrc/comm.cu) relies on:
 
 * ``shard``      rank r takes a contiguous block of the genome list (a genome never splits: an edge
                  label belongs to one genome, so edges never move between ranks);
-* ``owner``      the rank that deduplicates a node key: ``mix64(code) % world`` (murmur3 finaliser,
-                 the same function as csrc/common.cuh:mix64);
+* ``owner``      the rank that deduplicates a node key: the key space is cut into ``world`` equal
+                 ranges (csrc/comm.cu:range_owner), so the owned sets concatenate to the sorted table;
 * ``attach``     hands every rank the same 128-byte NCCL id through ``torch.distributed`` (NCCL on
                  the GPU box, gloo in the CPU tests) and opens the library's communicator;
 * ``reduce_counts``  whole-job edge / k-mer counts (nodes are already global after ``save()``).
@@ -42,9 +42,16 @@ def mix64(codes):
     return x
 
 
-def owner(codes, world):
-    """Owner rank of every node key."""
-    return (mix64(codes) % np.uint64(world)).astype(np.int64)
+def owner(codes, world, k):
+    """Owner rank of every node key (csrc/comm.cu:range_owner): equal slices of the 2k-bit code space by
+    the top 16 bits; opaque keys (bit 63) belong to the last rank."""
+    x = np.ascontiguousarray(codes, dtype=np.uint64)
+    bits = 2 * int(k)
+    t = (x >> np.uint64(bits - 16)) if bits >= 16 else (x << np.uint64(16 - bits))
+    t = np.minimum(t, np.uint64(0xffff))
+    o = ((t * np.uint64(world)) >> np.uint64(16)).astype(np.int64)
+    o[(x >> np.uint64(63)) != 0] = world - 1
+    return o
 
 
 def broadcast_bytes(buf, src=0, device=None):

@@ -113,6 +113,28 @@ class Engine(object):
         check(self.lib.pdg_emit_codes(self.h, int(begin), int(length), d.data_ptr()))
         return d[:n].cpu().numpy().view(np.uint64)
 
+    # ---- snapshot (pdg_snapshot_*, pdg_store_import) ----
+    def snapshot_export(self):
+        """dict of host arrays: the input of pdg_finalize (2-bit store, contigs, explicit part)"""
+        sz = (ctypes.c_uint64 * 4)()
+        check(self.lib.pdg_snapshot_sizes(self.h, sz))
+        n_res, n_c, n_e, n_n = (int(x) for x in sz)
+        words = np.zeros(max((n_res + 31) // 32, 1), dtype=np.uint64)
+        out = {"words": words, "c_begin": np.zeros(n_c, np.uint64), "c_len": np.zeros(n_c, np.uint64),
+               "c_type": np.zeros(n_c, np.uint32), "x_src": np.zeros(n_e, np.uint64), "x_tgt": np.zeros(n_e, np.uint64),
+               "x_type": np.zeros(n_e, np.uint32), "x_val": np.zeros(n_e, np.int32), "x_nodes": np.zeros(n_n, np.uint64)}
+        check(self.lib.pdg_snapshot_export(self.h, words.ctypes.data, words.size, *(
+            out[f].ctypes.data for f in ("c_begin", "c_len", "c_type", "x_src", "x_tgt", "x_type", "x_val", "x_nodes"))))
+        out["words"] = words[:(n_res + 31) // 32]
+        out["n_residues"] = n_res
+        return out
+
+    def store_import(self, words, n_residues):
+        words = _u64(words)
+        if words.size < (int(n_residues) + 31) // 32:
+            raise ValueError("store of %d residues needs %d words, got %d" % (n_residues, (n_residues + 31) // 32, words.size))
+        check(self.lib.pdg_store_import(self.h, words.ctypes.data, int(n_residues)))
+
     # ---- per-edge API ----
     def add_edges(self, src, tgt, type_id, value):
         src, tgt = _u64(src), _u64(tgt)

@@ -52,15 +52,16 @@ def _worker(rank, world, port, k, out_dir):
         assert D.broadcast_bytes(uid, 0).tolist() == list(range(128))
         # node exchange, host mirror of comm.cu: bucket by owner -> all-to-all -> unique -> all-gather
         codes = np.array([codec.encode(v, k) for v in nodes], dtype=np.uint64)
-        own = D.owner(codes, world)
+        own = D.owner(codes, world, k)
         send = [codes[own == r] for r in range(world)]
         recv = [None] * world
         dist.all_gather_object(recv, send)                      # recv[src][dst]
         owned = np.unique(np.concatenate([recv[src][rank] for src in range(world)]))
-        assert (D.owner(owned, world) == rank).all()
+        assert (D.owner(owned, world, k) == rank).all()
         gathered = [None] * world
         dist.all_gather_object(gathered, owned)
-        table = np.sort(np.concatenate(gathered))
+        table = np.concatenate(gathered)                        # ranges ascend with the rank: already sorted
+        assert (np.diff(table.astype(np.int64)) > 0).all()
         assert np.unique(table).size == table.size              # owned sets are disjoint
         tot_edges, tot_kmers = D.reduce_counts([len(edges), n_kmers])
         all_edges = [None] * world
@@ -87,14 +88,21 @@ def test_shard_covers_every_genome_once():
             assert max(map(len, parts)) - min(map(len, parts)) <= 1
 
 
-def test_owner_is_a_partition_and_matches_the_device_hash():
+def test_owner_is_a_monotone_partition():
+    """range partition of csrc/comm.cu:range_owner: monotone in the key (owned sets are ranges), balanced
+    on uniform codes, opaque keys on the last rank; mix64 keeps its known answers (edge checksums use it)"""
     from prairiedog_b200 import distributed as D
-    codes = np.arange(0, 1 << 16, dtype=np.uint64) * np.uint64(2654435761)
-    for w in (1, 2, 4, 8):
-        o = D.owner(codes, w)
-        assert o.min() >= 0 and o.max() < w
-        assert np.bincount(o, minlength=w).min() > codes.size // (2 * w)
-    # known answers of the murmur3 finaliser (same constants as csrc/common.cuh:mix64)
+    rng = np.random.default_rng(3)
+    for k in (5, 8, 11, 16, 31):
+        codes = np.sort(rng.integers(0, 1 << (2 * k), size=1 << 14, dtype=np.uint64))
+        for w in (1, 2, 3, 4, 8):
+            o = D.owner(codes, w, k)
+            assert o.min() >= 0 and o.max() < w
+            assert (np.diff(o) >= 0).all()
+            if k >= 8:
+                assert np.bincount(o, minlength=w).min() > codes.size // (2 * w)
+    opaque = np.array([(1 << 63) | 5, 7], dtype=np.uint64)
+    assert D.owner(opaque, 4, 11).tolist() == [3, 0]
     assert int(D.mix64(np.array([0], dtype=np.uint64))[0]) == 0
     assert int(D.mix64(np.array([1], dtype=np.uint64))[0]) == 0xb456bcfc34c2cb2c
 
