@@ -195,7 +195,10 @@ int pdg_get_build_stats(pdg_graph *g, pdg_build_stats *out);
 /* LGGraph.nodes / edges (lemon_graph.py:133-149).  Outputs are HOST arrays sized from
  * pdg_counts.  Nodes come in ascending code order (dense node id = index).  Edges: first the
  * genome part in index order (ascending (src code, position)), then the explicit part in CSR
- * order.  Any output pointer may be NULL. */
+ * order.  Any output pointer may be NULL.
+ * In a multi-rank job (pdg_comm_init) pdg_finalize leaves the global node table distributed over the
+ * ranks (every rank knows the global node COUNT); pdg_export_nodes, pdg_node_ids and pdg_checksum
+ * gather it on their first call after pdg_finalize, so that call is COLLECTIVE: every rank makes it. */
 int pdg_export_nodes(pdg_graph *g, uint64_t *h_codes);
 int pdg_export_edges(pdg_graph *g, uint64_t *h_src_code, uint64_t *h_tgt_code,
                      uint32_t *h_type_id, int32_t *h_value);

@@ -69,7 +69,11 @@ class B200Graph(Graph):
 
     # ------------------------------------------------------------------ interning
     def _key(self, value, create=True):
-        """Device key of a node value: the k-mer code, or an opaque id with bit 63 set."""
+        """Device key of a node value: the k-mer code, or an opaque id with bit 63 set.  Like LGGraph,
+        whose store keeps str(value), a non-string value (the int labels of encode=True,
+        subgraph_ref.py:54,65) reads back as its string."""
+        if not isinstance(value, str):
+            value = str(value)
         code = codec.encode(value, self.k)
         if code is not None:
             return code

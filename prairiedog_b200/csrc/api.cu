@@ -310,6 +310,10 @@ static int need_final(pdg_graph *g, const char *who) {
 int pdg_export_nodes(pdg_graph *g, uint64_t *h_codes) {
     PDG_API_BEGIN
     if (need_final(g, "pdg_export_nodes")) return PDG_E_INVALID;
+    if (g->u_lazy) {   // multi-rank: collective on the first call after pdg_finalize
+        const int rc = comm_materialize_nodes(g);
+        if (rc != PDG_OK) return rc;
+    }
     if (h_codes && g->n_nodes)
         PDG_CUDA(cudaMemcpyAsync(h_codes, g->u_codes, g->n_nodes * 8, cudaMemcpyDeviceToHost, g->stream));
     PDG_CUDA(cudaStreamSynchronize(g->stream));

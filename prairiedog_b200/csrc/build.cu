@@ -33,6 +33,7 @@ int finalize(pdg_graph *g, int flags) {
     Timer total(s), lap(s);
     g->stats = pdg_build_stats{};
     g->finalized = false;
+    g->u_lazy = false;
     const int k = g->k;
     if (g->n_res >= (1ULL << 32)) {
         set_error("pdg_finalize: %llu residues exceed the 32-bit position column", (unsigned long long)g->n_res);
@@ -95,7 +96,8 @@ int finalize(pdg_graph *g, int flags) {
     }
     g->n_nodes = n_local;
     if (g->world > 1) {
-        // K5: hash-partitioned exchange of the node keys; every rank ends with the global table
+        // K5: range-partitioned exchange of the node keys; every rank learns the global node count, the
+        // global table is gathered on demand (comm_materialize_nodes)
         uint64_t n_glob = 0;
         // opaque node keys of the explicit part carry bit 63; clean k-mer codes need 2k bits
         const int rc = comm_global_nodes(g, g->u_codes, n_local, g->x_n_nodes ? 64 : 2 * k, &n_glob);

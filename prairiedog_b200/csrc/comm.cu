@@ -161,6 +161,8 @@ static int comm_global_nodes_bitmap(pdg_graph *g, NcclApi *api, uint64_t *n_glob
     return PDG_OK;
 }
 
+int comm_materialize_nodes(pdg_graph *g);
+
 // In: d_local holds this rank's sorted unique codes (n_loc of them; may alias g->u_codes_buf).
 // Out: g->u_codes_buf holds the global sorted unique table, *n_global its size.
 int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int key_bits, uint64_t *n_global) {
@@ -173,6 +175,7 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
     cudaStream_t s = g->stream;
     ncclComm_t comm = reinterpret_cast<ncclComm_t>(g->nccl_comm);
     const int W = g->world, R = g->rank;
+    g->u_lazy = false;
 
     // 0. agree on the path: every rank reports {words of its presence bitmap or 0, key bits it needs}
     {
@@ -245,25 +248,50 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
                                                          g->scratch1.as<uint64_t>(), n_recv, d_own.as<uint64_t>());
         PDG_LAUNCHED(g);
     }
-    // 4. all-gather the owned sets in rank order: ranges ascend with the rank, so this IS the sorted
-    //    global table
+    // 4. sizes of the owned sets -> global node count.  The table itself (the owned sets in rank order:
+    //    ranges ascend with the rank, so their concatenation IS the sorted global table) is gathered
+    //    only when something asks for it (comm_materialize_nodes): its size grows with the whole job,
+    //    not with this rank's share, and a build does not need it.
     PDG_CUDA(cudaMemcpyAsync(counts, &n_own, 8, cudaMemcpyHostToDevice, s));
     PDG_NCCL(api, api->AllGather(counts, d_all_counts.p, 1, ncclUint64, comm, s));
-    std::vector<uint64_t> own_counts(W);
-    PDG_CUDA(cudaMemcpyAsync(own_counts.data(), d_all_counts.p, W * 8, cudaMemcpyDeviceToHost, s));
-    PDG_CUDA(cudaStreamSynchronize(s));   // the sends are done: d_local (which may live in u_codes_buf) is no longer read
+    g->c_own_counts.assign(W, 0);
+    PDG_CUDA(cudaMemcpyAsync(g->c_own_counts.data(), d_all_counts.p, W * 8, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));   // the sends are done: d_local is no longer read
+    uint64_t n_glob = 0;
+    for (int p = 0; p < W; ++p) n_glob += g->c_own_counts[p];
+    g->u_lazy = true;
+    static const bool eager = getenv("PDG_EAGER_NODE_TABLE") != nullptr;
+    if (eager) {
+        const int rc = comm_materialize_nodes(g);
+        if (rc != PDG_OK) return rc;
+    }
+    *n_global = n_glob;
+    return PDG_OK;
+}
+
+// Collective: every rank of the job has to call it (pdg_export_nodes, pdg_node_ids and pdg_checksum
+// do, on their first call after a multi-rank pdg_finalize).
+int comm_materialize_nodes(pdg_graph *g) {
+    if (!g->u_lazy) return PDG_OK;
+    NcclApi *api = nccl_api();
+    if (!api) return PDG_E_COMM;
+    cudaStream_t s = g->stream;
+    ncclComm_t comm = reinterpret_cast<ncclComm_t>(g->nccl_comm);
+    const int W = g->world;
     std::vector<uint64_t> own_off(W + 1, 0);
-    for (int p = 0; p < W; ++p) own_off[p + 1] = own_off[p] + own_counts[p];
+    for (int p = 0; p < W; ++p) own_off[p + 1] = own_off[p] + g->c_own_counts[p];
     const uint64_t n_glob = own_off[W];
+    PDG_CUDA(cudaStreamSynchronize(s));
     g->u_codes_buf.reserve(std::max<size_t>(n_glob * 8, 16), s);
     PDG_NCCL(api, api->GroupStart());
     for (int p = 0; p < W; ++p)
-        if (own_counts[p])
-            PDG_NCCL(api, api->Broadcast(d_own.p, g->u_codes_buf.as<uint64_t>() + own_off[p], own_counts[p], ncclUint64, p,
-                                         comm, s));
+        if (g->c_own_counts[p])
+            PDG_NCCL(api, api->Broadcast(g->c_own.p, g->u_codes_buf.as<uint64_t>() + own_off[p], g->c_own_counts[p],
+                                         ncclUint64, p, comm, s));
     PDG_NCCL(api, api->GroupEnd());
     PDG_CUDA(cudaStreamSynchronize(s));
-    *n_global = n_glob;
+    g->u_codes = g->u_codes_buf.as<uint64_t>();
+    g->u_lazy = false;
     return PDG_OK;
 }
 

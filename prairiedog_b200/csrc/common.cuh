@@ -183,6 +183,8 @@ struct pdg_graph {
 
     // ---- multi GPU ----
     pdg::DevBuf c_counts, c_all_counts, c_send, c_recv, c_own, c_tmp, c_all, c_all2;   // comm.cu scratch
+    std::vector<uint64_t> c_own_counts;   // size of every rank's owned node set
+    bool u_lazy = false;                  // multi-rank: the global node table is not gathered yet (comm_materialize_nodes)
     void *nccl_comm = nullptr;
     int rank = 0, world = 1;
 };
@@ -235,5 +237,7 @@ int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_
 // in: sorted unique codes of this rank (d_local, n_local); out: g->u_codes_buf holds the global
 // sorted unique table of all ranks, *n_global its size
 int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_local, int key_bits, uint64_t *n_global);
+// collective: gathers the global sorted node table into g->u_codes_buf if it is still distributed
+int comm_materialize_nodes(pdg_graph *g);
 
 }  // namespace pdg

@@ -146,6 +146,10 @@ int export_edges(pdg_graph *g, uint64_t *h_src, uint64_t *h_tgt, uint32_t *h_typ
 
 int checksum(pdg_graph *g, uint64_t *nodes_sum, uint64_t *edges_sum) {
     cudaStream_t s = g->stream;
+    if (g->u_lazy) {   // multi-rank: collective on the first call after pdg_finalize
+        const int rc = comm_materialize_nodes(g);
+        if (rc != PDG_OK) return rc;
+    }
     DevBuf d;
     d.reserve(32, s);
     PDG_CUDA(cudaMemsetAsync(d.p, 0, 32, s));

@@ -130,6 +130,10 @@ int fetch_residues(pdg_graph *g, uint64_t begin, uint64_t len, uint8_t *h_ascii)
 
 int node_ids(pdg_graph *g, const uint64_t *h_codes, uint64_t n, uint64_t *h_ids) {
     cudaStream_t s = g->stream;
+    if (g->u_lazy) {   // multi-rank: collective on the first call after pdg_finalize (before the n == 0 exit)
+        const int rc = comm_materialize_nodes(g);
+        if (rc != PDG_OK) return rc;
+    }
     if (n == 0) return PDG_OK;
     DevBuf dc, di;
     dc.reserve(n * 8, s);

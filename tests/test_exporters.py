@@ -65,3 +65,29 @@ def test_snapshot_container_round_trip(tmp_path):
         assert False
     except ValueError:
         pass
+
+
+def test_graph_ref_mic_labels_and_first_seen_ids(tmp_path):
+    """graph_ref.py:20-103 / gref.py:9-19: MIC values get ids from 1 in first-seen order, k-mers and
+    files from 0; one-hot rows"""
+    from prairiedog_b200.graph_ref import GraphRef
+
+    class _Km:
+        def __init__(self, p, u):
+            self.filepath, self.unique_kmers = p, u
+    csv = tmp_path / "mic.csv"
+    csv.write_text("run,AMP,CIP\nSRR1,8.0,0.5\nSRR2,>=32,0.5\n")
+    gr = GraphRef(str(csv))
+    a, b = _Km("samples/SRR1.fasta", 10), _Km("x/SRR2.fa", 30)
+    gr._record_graph_label(a)
+    gr._record_graph_label(b)
+    assert gr.mic_map == {"8.0": 1, "0.5": 2, ">=32": 3} or list(gr.mic_map.values()) == [1, 2, 3]
+    assert gr.get_graph_label(b, "CIP") == gr.get_graph_label(a, "CIP")
+    assert gr.get_graph_label(b, "AMP") == 3
+    gr.index_kmers(a)
+    gr.index_kmers(b)
+    assert gr.max_num_nodes == 30
+    assert [gr.node_label(x) for x in ("ATC", "TCG", "ATC")] == [0, 1, 0]
+    assert gr.edge_label(a) == 0 and gr.edge_label(b) == 1 and gr.edge_label(a) == 0
+    assert GraphRef._one_hot(2, 4).tolist() == [0, 0, 1, 0]
+    assert GraphRef(None).MIC_DF is None

@@ -135,3 +135,24 @@ def test_cli_pangenome_query_and_batch(tmp_path):
     assert r.exit_code == 0 and "{} edges".format(len(case["edges"])) in r.output
     r = CliRunner().invoke(cli.cli, ["query", src, tgt, "--backend", "dgraph", "--graph", out])
     assert r.exit_code != 0
+
+
+@pytest.mark.parametrize("name", ["15_k11", "syn_k5"])
+def test_update_graph_encode_true_matches_reference(name):
+    """SURVEY.md 8f rank 4: encode=True labels nodes by first-seen k-mer id (graph_ref.py:97-99);
+    golden from the reference's LGGraph (tests/golden/make_encode_golden.py)"""
+    from prairiedog_b200 import B200Graph, Kmers, SubgraphRef, GraphRef
+    case = golden("encode.json")[name]
+    g = B200Graph(k=case["k"])
+    sg, gr = SubgraphRef(g), GraphRef()
+    returned = []
+    for f in case["files"]:
+        km = Kmers(data_path(f), case["k"])
+        gr.index_kmers(km)
+        returned.append(sg.update_graph(km, gr, encode=True))
+        sg.save()
+    assert returned == case["returned"]
+    assert gr.kmer_map == case["kmer_map"]
+    nodes, edges = g.canonical()
+    assert [repr(n) for n in nodes] == case["nodes"]
+    assert [[repr(e[0]), repr(e[1]), e[2], e[3]] for e in edges] == case["edges"]
