@@ -343,11 +343,14 @@ def kernel_table(st, k, peak):
         t = traffic.get(name.split(" ")[0])
         rows.append({"kernel": name, "ms_per_launch": ms, "units": units, "bytes_per_unit": bpu, "bytes": units * bpu,
                      "achieved": ach, "frac": ach / peak, "traffic": (t * units) if t is not None else None})
-    if k <= 11 and st["ms_pass"][0] > 0:
+    if st["ms_pass"][0] > 0:     # msd3 on the whole code (k <= 11) or on the 11-residue prefix (k > 16)
         add("m3_pass1_kernel (packed genome -> records grouped by digit 3)", st["ms_pass"][0], n, 8.25)
         add("m3_pass2_kernel (records -> grouped by digits 3,2)", st["ms_pass"][1], n, 16.0)
         add("m3_pass3_kernel (records -> row starts + position column)", st["ms_pass"][2], n, 12.0)
         add("m3_hist_kernel (joint digit histograms from the packed genome)", st["ms_hist"], n, 0.25)
+        if k > 11 and st["ms_sort_kernel_avg"] > 0:
+            # reads a position, gathers the two packed words of its code, writes a 16-byte record
+            add("ml_bucket_sort_kernel (prefix buckets -> records sorted on the full code)", st["ms_sort_kernel_avg"], n, 36.0)
     elif st["ms_sort_kernel_avg"] > 0:
         add("onesweep_kernel (one LSD partition pass)", st["ms_sort_kernel_avg"], n, 16.0 if k <= 16 else 32.0)
     add("fb_summ_kernel (FASTA bytes -> tile summaries)", st["ms_ingest_a"], nb, 1.0)

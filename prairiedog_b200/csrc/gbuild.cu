@@ -51,15 +51,19 @@ __global__ void g_popc_words_kernel(const uint32_t *__restrict__ bm, uint64_t n_
     if (i < n_words) cnt[i] = __popc(bm[i]);
 }
 
+// head_flags: one word per record, 1 where a new code starts (computed here when null)
 template <typename Rec>
-static void rows_from_sorted(pdg_graph *g, const Rec *sorted, uint64_t n) {
+static void rows_from_sorted(pdg_graph *g, const Rec *sorted, uint64_t n, const uint32_t *head_flags = nullptr) {
     cudaStream_t s = g->stream;
-    g->scratch0.reserve(n * 4, s);
     g->scratch1.reserve((n + 1) * 4, s);
-    uint32_t *flg = g->scratch0.as<uint32_t>();
     uint32_t *rank = g->scratch1.as<uint32_t>();
-    g_head_flags_kernel<Rec><<<grid_for(n, 256), 256, 0, s>>>(sorted, n, flg);
-    PDG_LAUNCHED(g);
+    const uint32_t *flg = head_flags;
+    if (!flg) {
+        g->scratch0.reserve(n * 4, s);
+        g_head_flags_kernel<Rec><<<grid_for(n, 256), 256, 0, s>>>(sorted, n, g->scratch0.as<uint32_t>());
+        PDG_LAUNCHED(g);
+        flg = g->scratch0.as<uint32_t>();
+    }
     exclusive_scan_u32_u32(flg, rank, n, g);
     uint32_t nn = 0;
     PDG_CUDA(cudaMemcpyAsync(&nn, rank + n, 4, cudaMemcpyDeviceToHost, s));
@@ -87,6 +91,7 @@ void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, i
     if (n == 0) return;
     TraverseOut out;
     uint64_t passes = 0;
+    const uint32_t *ml_heads = nullptr;
     g->collect_sort_stats = true;
     if (k <= 16) {
         // fused path (ksort.cu): the first pass reads the packed genome, the last writes positions
@@ -101,6 +106,9 @@ void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, i
             g->stats.pipelined = staged ? 1 : 0;
         }
         else if (!ksort_build(g, ct, hc, &sorted)) rows_from_sorted<uint64_t>(g, sorted, n);
+        passes = g->stats.sort_passes;
+    } else if (const uint4 *srt = nullptr; !(flags & PDG_F_FORCE_SORT_NODES) && msdlong_build(g, ct, hc, &srt, &ml_heads)) {
+        rows_from_sorted<uint4>(g, srt, n, ml_heads);   // msdlong.cu: prefix MSD + bucket sort
         passes = g->stats.sort_passes;
     } else {
         g->recA.reserve(n * 16, s);

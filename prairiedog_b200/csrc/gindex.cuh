@@ -47,9 +47,14 @@ void msd3_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc);
 // the same build in steps (groups of positions staged one by one, ingest_batch.cu)
 void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_groups);
 void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64_t pos1);
-void msd3_finish_launch(pdg_graph *g);                 // pass 3 + presence + ranks, asynchronous
+void msd3_finish_launch(pdg_graph *g, bool rows = true);                 // pass 3 + presence + ranks, asynchronous
 void msd3_finish_complete(pdg_graph *g, uint64_t n_kmers);
 void msd3_finish(pdg_graph *g, uint64_t n_kmers);      // launch (unless already launched) + complete
+
+// msdlong.cu: 17 <= k <= 31: msd3 on the 11-residue prefix + a shared-memory sort of every bucket;
+// false = not applicable / a bucket did not fit (the caller runs the LSD sort of radix.cu)
+bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, const uint4 **sorted,
+                   const uint32_t **head_flags);
 
 // xbuild.cu: builds the explicit part from g->x_* plus the demoted contigs
 void build_x_part(pdg_graph *g, const HostContigs &demoted);

@@ -29,12 +29,12 @@ struct M3Plan {
 // ---- per-tile contig lookup ----------------------------------------------------------------------
 // tile_info[tile] = index of the last contig that begins at or before the tile (0 if none), with
 // M3_SIMPLE set when every window of the tile is a k-mer of that contig.
-__global__ void m3_tile_info_kernel(ContigTable ct, M3Plan pl, int k, uint32_t *__restrict__ tile_info) {
+__global__ void m3_tile_info_kernel(ContigTable ct, M3Plan pl, int kv, uint32_t *__restrict__ tile_info) {
     const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
     if (tile >= pl.n_tiles) return;
     const uint64_t p0 = pl.base0 + (uint64_t)tile * M3_TILE;
     const uint64_t ci = contig_of(ct, p0);
-    const bool simple = p0 >= ct.begin[ci] && p0 + M3_TILE - 1 + k <= ct.end[ci];
+    const bool simple = p0 >= ct.begin[ci] && p0 + M3_TILE - 1 + kv <= ct.end[ci];
     tile_info[tile] = (uint32_t)ci | (simple ? M3_SIMPLE : 0u);
 }
 
@@ -46,7 +46,7 @@ __global__ void m3_tile_info_kernel(ContigTable ct, M3Plan pl, int k, uint32_t *
 static constexpr int M3H_THREADS = 1024;
 static constexpr int M3H_WARPS = M3H_THREADS / 32;
 __global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const uint2 *__restrict__ packed, uint64_t packed_words,
-                                                              int k, ContigTable ct, M3Plan pl,
+                                                              int k, int kv, ContigTable ct, M3Plan pl,
                                                               const uint32_t *__restrict__ tile_info,
                                                               uint32_t *__restrict__ H1T, uint32_t *__restrict__ H12,
                                                               unsigned int *__restrict__ tot32) {
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const uint2 *__res
         for (int i = lane; i < 128; i += 32) h1[w][i] = 0;
         const bool simple = (info & M3_SIMPLE) != 0;
         if (!simple)
-            for (int i = lane; i < M3_TILE_WORDS; i += 32) vms[w][i] = m3_valid_word(ct, w0 + i, info & ~M3_SIMPLE, k);
+            for (int i = lane; i < M3_TILE_WORDS; i += 32) vms[w][i] = m3_valid_word(ct, w0 + i, info & ~M3_SIMPLE, kv);
         __syncwarp();
         // lane l keeps packed words w0 + 32*g + l for the current group g of 32 rounds
         for (int g = 0; g < M3_TILE_WORDS / 32; ++g) {
@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(256) m3_scan_chunks_kernel(uint32_t *__restric
 // ---- pass 1: position tile -> records grouped by d3 ---------------------------------------------
 template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uint2 *__restrict__ packed,
-                                                                 uint64_t packed_words, int k, ContigTable ct, M3Plan pl,
+                                                                 uint64_t packed_words, int k, int kv, ContigTable ct, M3Plan pl,
                                                                  const uint32_t *__restrict__ tile_info,
                                                                  const uint32_t *__restrict__ O1T,
                                                                  uint64_t *__restrict__ out) {
@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uin
         words[i] = w0 + i < packed_words ? packed[w0 + i] : make_uint2(0u, 0u);
     static_assert(M3_TILE_WORDS <= M3_THREADS, "one validity word per thread");
     if (tid < M3_TILE_WORDS)
-        vm[tid] = (info & M3_SIMPLE) ? 0xffffffffu : m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, k);
+        vm[tid] = (info & M3_SIMPLE) ? 0xffffffffu : m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, kv);
     for (uint32_t b = tid; b < B3; b += M3_THREADS) sm.cursor[b] = O1T[(size_t)b * pl.n_tiles + tile];
     m3_clear_table(sm);
     __syncthreads();
@@ -394,7 +394,8 @@ static M3Plan m3_plan(int k, uint64_t pos0, uint64_t pos1) {
 
 void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_groups) {
     cudaStream_t s = g->stream;
-    const int k = g->k;
+    const int kv = g->k, k = std::min(g->k, kMsd3MaxBits / 2);   // sort key: the first k residues of a kv-mer
+    (void)kv;
     const M3Plan pl = m3_plan(k, pos_lo, pos_hi);
     const uint32_t B3 = 1u << pl.b3, cells = 1u << (pl.b3 + pl.b2);
     const uint64_t n_codes = 1ULL << (2 * k), n = pos_hi - pos_lo;
@@ -424,7 +425,8 @@ void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_g
 
 void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64_t pos1) {
     cudaStream_t s = g->stream;
-    const int k = g->k;
+    const int kv = g->k, k = std::min(g->k, kMsd3MaxBits / 2);   // sort key: the first k residues of a kv-mer
+    (void)kv;
     if (g->m3_groups.size() >= g->m3_max_groups) {
         set_error("msd3_stage_group: more than %u groups", g->m3_max_groups);
         throw CudaError{PDG_E_INVALID};
@@ -440,7 +442,7 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
     PDG_CUDA(cudaMemsetAsync(tot32, 0, cells * 4, s));
     const uint2 *packed = g->packed.as<uint2>();
     const uint64_t pw = g->packed.cap / 8;
-    m3_tile_info_kernel<<<(pl.n_tiles + 255) / 256, 256, 0, s>>>(ct, pl, k, tile_info);
+    m3_tile_info_kernel<<<(pl.n_tiles + 255) / 256, 256, 0, s>>>(ct, pl, kv, tile_info);
     PDG_LAUNCHED(g);
     // CUDA events around every launch of the sort (bench.py's roofline numbers): event i precedes
     // stage i of {hist, scans, pass 1, pass 2, pass 3}
@@ -453,7 +455,7 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
         }
     auto mark = [&](int i) { if (timed) PDG_CUDA(cudaEventRecord(g->k_events[i], s)); };
     mark(0);
-    m3_hist_kernel<<<pl.n_chunks, M3H_THREADS, cells * 4, s>>>(packed, pw, k, ct, pl, tile_info, H1T, H12, tot32);
+    m3_hist_kernel<<<pl.n_chunks, M3H_THREADS, cells * 4, s>>>(packed, pw, k, kv, ct, pl, tile_info, H1T, H12, tot32);
     PDG_LAUNCHED(g);
     mark(1);
     uint32_t *goff = g->m3_gbase.as<uint32_t>() + (size_t)g->m3_max_groups * (cells + 1);
@@ -464,7 +466,7 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
     m3_scan_tiles_kernel<<<pl.n_chunks, 256, 0, s>>>(H1T, pl, H12, base32);
     PDG_LAUNCHED(g);
     mark(2);
-    m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, ct, pl, tile_info, H1T,
+    m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, kv, ct, pl, tile_info, H1T,
                                                                      g->recA.as<uint64_t>() + rec_off);
     PDG_LAUNCHED(g);
     mark(3);
@@ -479,9 +481,10 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
 // Pass 3 + presence + ranks, all asynchronous on the graph's stream: a pipelined ingest launches
 // this speculatively when its last group is staged, so that it runs while the caller declares
 // the contigs.  msd3_finish_complete reads the node count back and writes the rows.
-void msd3_finish_launch(pdg_graph *g) {
+void msd3_finish_launch(pdg_graph *g, bool rows) {
     cudaStream_t s = g->stream;
-    const int k = g->k;
+    const int kv = g->k, k = std::min(g->k, kMsd3MaxBits / 2);   // sort key: the first k residues of a kv-mer
+    (void)kv;
     const M3Plan pl = m3_plan(k, 0, 32);   // digit widths only
     const uint32_t cells = 1u << (pl.b3 + pl.b2);
     const uint32_t G = (uint32_t)g->m3_groups.size();
@@ -506,6 +509,7 @@ void msd3_finish_launch(pdg_graph *g) {
         PDG_CUDA(cudaEventRecord(g->k_events[5], s));
     // sentinel: rowtab[n_codes] = number of records (= base of the cell past the last)
     PDG_CUDA(cudaMemcpyAsync(rowtab + n_codes, base32 + cells, 4, cudaMemcpyDeviceToDevice, s));
+    if (!rows) return;   // k > 11 (msdlong.cu): the buckets of the 11-residue prefix are finished there
     // rows: presence -> rank
     uint32_t *flags = g->recA.as<uint32_t>(), *rank = g->scratch1.as<uint32_t>();
     m3_present_kernel<<<grid_for(n_codes, 256), 256, 0, s>>>(rowtab, n_codes, flags);
@@ -516,7 +520,8 @@ void msd3_finish_launch(pdg_graph *g) {
 
 void msd3_finish_complete(pdg_graph *g, uint64_t n) {
     cudaStream_t s = g->stream;
-    const int k = g->k;
+    const int kv = g->k, k = std::min(g->k, kMsd3MaxBits / 2);   // sort key: the first k residues of a kv-mer
+    (void)kv;
     const uint32_t G = (uint32_t)g->m3_groups.size();
     const uint64_t n_codes = 1ULL << (2 * k);
     uint32_t *rowtab = g->scratch0.as<uint32_t>();
@@ -549,7 +554,7 @@ void msd3_finish_complete(pdg_graph *g, uint64_t n) {
 }
 
 void msd3_finish(pdg_graph *g, uint64_t n) {
-    if (!g->m3_launched) msd3_finish_launch(g);
+    if (!g->m3_launched) msd3_finish_launch(g, true);
     msd3_finish_complete(g, n);
 }
 

@@ -79,3 +79,50 @@ def test_batch_order_does_not_change_the_graph():
     assert g1.engine.checksum()[0] == g2.engine.checksum()[0]          # node set checksum
     assert np.array_equal(g1.engine.export_nodes(), g2.engine.export_nodes())
     assert g1.canonical() == g2.canonical()
+
+
+@pytest.mark.parametrize("k", [17, 23, 31])
+def test_long_k_prefix_path_equals_lsd_path_and_oracle(k):
+    """k > 16 (msdlong.cu: MSD on the 11-residue prefix + window sort) against the C oracle and against
+    the LSD sort of 128-bit records it replaces (PDG_F_FORCE_SORT_NODES)"""
+    from oracle.c_oracle import COracle
+    from prairiedog_b200 import B200Graph, _ffi
+    files = _genomes(3, n_bases=1_000_000, n_contigs=40)
+    g, _ = _build(k, files)
+    assert g.engine.stats()["sort_passes"] == 4                       # the prefix path ran
+    o = COracle(k)
+    for _, buf, _ in files:
+        o.add_fasta_bytes(buf)
+    o.build()
+    assert g.engine.counts() == o.counts()
+    assert g.engine.checksum() == o.checksum()
+    for got, want in zip(g.engine.export_index(), o.index()):
+        assert np.array_equal(got, want)
+    h = B200Graph(k=k)
+    h.add_fasta_batch(files)
+    h._flush()
+    h.engine.finalize(_ffi.PDG_F_FORCE_SORT_NODES)
+    assert h.engine.stats()["sort_passes"] != 4
+    for got, want in zip(g.engine.export_index(), h.engine.export_index()):
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("run,prefix_path", [(3_000, True), (20_000, False)])
+def test_long_k_low_complexity(run, prefix_path):
+    """a poly-A run puts `run` positions into one prefix bucket.  3 000: larger than a window, sorted by the
+    big-bucket kernel; 20 000: larger than that kernel's shared memory, the build takes the LSD path.
+    The answer stays exact either way."""
+    from oracle.c_oracle import COracle
+    rng = np.random.default_rng(11)
+    seq = bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=30_000)) + b"A" * run + \
+        bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=10_000))
+    lines = [seq[i:i + 80] for i in range(0, len(seq), 80)]
+    img = np.frombuffer(b">repeat\n" + b"\n".join(lines) + b"\n", dtype=np.uint8)
+    g, _ = _build(21, [("rep.fasta", img, None)])
+    assert (g.engine.stats()["sort_passes"] == 4) == prefix_path
+    o = COracle(21)
+    o.add_fasta_bytes(img)
+    o.build()
+    assert g.engine.counts() == o.counts()
+    for got, want in zip(g.engine.export_index(), o.index()):
+        assert np.array_equal(got, want)
