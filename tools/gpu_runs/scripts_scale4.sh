@@ -1,0 +1,10 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_multi_rank.py -m gpu -x -q > gpurun_out/pytest_multi.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_multi.log
+timeout 600 python bench.py --gpus 1 --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/scale_n1.log 2>&1; echo "exit $?" >> gpurun_out/scale_n1.log
+timeout 600 python bench.py --gpus 1 --k 31 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/scale_k31_n1.log 2>&1; echo "exit $?" >> gpurun_out/scale_k31_n1.log
+for n in 2 4 8; do
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500+n)) bench.py --gpus $n --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/scale_n$n.log 2>&1; echo "exit $?" >> gpurun_out/scale_n$n.log
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29600+n)) bench.py --gpus $n --k 31 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/scale_k31_n$n.log 2>&1; echo "exit $?" >> gpurun_out/scale_k31_n$n.log
+done
+for f in pytest_multi scale_n1 scale_n2 scale_n4 scale_n8 scale_k31_n1 scale_k31_n2 scale_k31_n4 scale_k31_n8; do echo "== $f"; tail -n 2 gpurun_out/$f.log | cut -c1-200; done
