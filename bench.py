@@ -40,12 +40,16 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample-bases", type=int, default=1_500_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--iid", action="store_true",
+                    help="every genome independent i.i.d. random (worst case for deduplication, SURVEY.md 8d) instead of "
+                         "substitutions / indels of one base genome")
     return ap.parse_args()
 
 
 def workload_config(a):
-    return {"workload": "config3: %d synthetic E. coli-like genomes per GPU (%.1f Mbp, %d contigs each), k=%d, "
-                        "one pangenome" % (a.genomes, a.bases / 1e6, a.contigs, a.k),
+    return {"workload": "config3: %d synthetic %s genomes per GPU (%.1f Mbp, %d contigs each), k=%d, "
+                        "one pangenome" % (a.genomes, "independent i.i.d. random" if a.iid else "E. coli-like", a.bases / 1e6,
+                                           a.contigs, a.k),
             "genomes_per_gpu": a.genomes, "bases_per_genome": a.bases, "contigs_per_genome": a.contigs, "k": a.k,
             "l2": "inputs (%.0f MB of FASTA per step) exceed the 126 MB L2" % (a.genomes * a.bases * 1.0127 / 1e6)}
 
@@ -59,7 +63,7 @@ def cpu_reference(a, sample_bases):
     n_gen = max(1, -(-sample_bases // a.bases))
     tmp = tempfile.mkdtemp(prefix="pdg_cpu_")
     paths, total = [], 0
-    for name, buf, lens in synth.genomes(n_gen, n_bases=a.bases, n_contigs=a.contigs):
+    for name, buf, lens in synth.genomes(n_gen, n_bases=a.bases, n_contigs=a.contigs, related=not a.iid):
         p = os.path.join(tmp, name)
         with open(p, "wb") as f:
             f.write(buf.tobytes())
@@ -229,7 +233,7 @@ def run_b200(a):
 
     # synthetic genomes of this rank: pinned host images and device-resident copies
     files, n_bases = [], 0
-    for name, buf, lens in synth.genomes(a.genomes, n_bases=a.bases, n_contigs=a.contigs, first=rank * a.genomes):
+    for name, buf, lens in synth.genomes(a.genomes, n_bases=a.bases, n_contigs=a.contigs, first=rank * a.genomes, related=not a.iid):
         pinned = torch.from_numpy(buf).pin_memory()
         files.append((name, pinned.numpy(), pinned.to(dev), pinned))
         n_bases += int(lens.sum())

@@ -183,7 +183,7 @@ struct pdg_graph {
     uint64_t ingest_bytes = 0, ingest_launches = 0;
 
     // ---- multi GPU ----
-    pdg::DevBuf c_counts, c_all_counts, c_send, c_recv, c_own, c_tmp, c_all, c_all2;   // comm.cu scratch
+    pdg::DevBuf c_counts, c_all_counts, c_recv, c_own, c_tmp, c_all, c_all2;   // comm.cu scratch
     std::vector<uint64_t> c_own_counts;   // size of every rank's owned node set
     bool u_lazy = false;                  // multi-rank: the global node table is not gathered yet (comm_materialize_nodes)
     void *nccl_comm = nullptr;

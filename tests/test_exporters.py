@@ -91,3 +91,12 @@ def test_graph_ref_mic_labels_and_first_seen_ids(tmp_path):
     assert gr.edge_label(a) == 0 and gr.edge_label(b) == 1 and gr.edge_label(a) == 0
     assert GraphRef._one_hot(2, 4).tolist() == [0, 0, 1, 0]
     assert GraphRef(None).MIC_DF is None
+
+
+def test_cli_sample_files_follow_the_snakefile(tmp_path):
+    """Snakefile:22-24: every *.fna / *.fasta / *.fa of the samples directory, nothing else; sorted so that
+    type ids are reproducible"""
+    from prairiedog_b200 import cli
+    for name in ("b.fasta", "a.fa", "c.fna", "notes.txt", "d.fasta.gz", "public_mic_class_dataframe.csv"):
+        (tmp_path / name).write_text(">x\nACGT\n")
+    assert [p.split("/")[-1] for p in cli.sample_files(str(tmp_path))] == ["a.fa", "b.fasta", "c.fna"]
