@@ -93,21 +93,22 @@ void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, i
     uint64_t passes = 0;
     const uint32_t *ml_heads = nullptr;
     g->collect_sort_stats = true;
+    // a pipelined ingest already ran passes 1-2 (and launched pass 3) group by group -- if the caller
+    // declared exactly the contigs it assumed, only the rest is left
+    bool staged = g->pre_valid && !g->m3_groups.empty() && g->pre_begin.size() == hc.size() &&
+                  !(flags & PDG_F_FORCE_SORT_NODES);
+    for (size_t i = 0; staged && i < hc.size(); ++i)
+        staged = g->pre_begin[i] == hc.begin[i] && g->pre_begin[i] + g->pre_len[i] == hc.end[i];
+    g->stats.pipelined = staged ? 1 : 0;
     if (k <= 16) {
         // fused path (ksort.cu): the first pass reads the packed genome, the last writes positions
         const uint64_t *sorted = nullptr;
         if (2 * k <= kMsd3MaxBits && !(flags & PDG_F_FORCE_SORT_NODES)) {   // msd3.cu
-            // a pipelined ingest already ran passes 1-2 group by group -- if the caller declared
-            // exactly the contigs it assumed, only pass 3 is left
-            bool staged = g->pre_valid && !g->m3_groups.empty() && g->pre_begin.size() == hc.size();
-            for (size_t i = 0; staged && i < hc.size(); ++i)
-                staged = g->pre_begin[i] == hc.begin[i] && g->pre_begin[i] + g->pre_len[i] == hc.end[i];
             if (staged) msd3_finish(g, n); else msd3_build(g, ct, hc);
-            g->stats.pipelined = staged ? 1 : 0;
         }
         else if (!ksort_build(g, ct, hc, &sorted)) rows_from_sorted<uint64_t>(g, sorted, n);
         passes = g->stats.sort_passes;
-    } else if (const uint4 *srt = nullptr; !(flags & PDG_F_FORCE_SORT_NODES) && msdlong_build(g, ct, hc, &srt, &ml_heads)) {
+    } else if (const uint4 *srt = nullptr; !(flags & PDG_F_FORCE_SORT_NODES) && msdlong_build(g, ct, hc, staged, &srt, &ml_heads)) {
         rows_from_sorted<uint4>(g, srt, n, ml_heads);   // msdlong.cu: prefix MSD + bucket sort
         passes = g->stats.sort_passes;
     } else {

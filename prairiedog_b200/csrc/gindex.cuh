@@ -53,7 +53,7 @@ void msd3_finish(pdg_graph *g, uint64_t n_kmers);      // launch (unless already
 
 // msdlong.cu: 17 <= k <= 31: msd3 on the 11-residue prefix + a shared-memory sort of every bucket;
 // false = not applicable / a bucket did not fit (the caller runs the LSD sort of radix.cu)
-bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, const uint4 **sorted,
+bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, bool staged, const uint4 **sorted,
                    const uint32_t **head_flags);
 
 // xbuild.cu: builds the explicit part from g->x_* plus the demoted contigs

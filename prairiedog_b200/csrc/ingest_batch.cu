@@ -368,15 +368,19 @@ __global__ void fb_hash_kernel(const FbFile *__restrict__ files, uint32_t f0, ui
 // declared exactly these contigs.
 __global__ void fb_contigs_kernel(const FbFile *__restrict__ files, uint32_t f0, uint32_t f1,
                                   const FbFileTotals *__restrict__ totals, uint64_t row_begin, uint64_t row_end,
-                                  const uint64_t *__restrict__ table, uint64_t *__restrict__ ct_begin,
+                                  const uint64_t *__restrict__ table, int k, uint64_t *__restrict__ ct_begin,
                                   uint64_t *__restrict__ ct_end) {
     const uint64_t r = row_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= row_end) return;
     const uint32_t f = fb_file_of_row(files, f0, f1, r);
     const FbFile fi = files[f];
     const bool last = r + 1 == fi.hdr_base + totals[f].hdr;
-    ct_begin[r] = fi.res_base + table[4 * r + 2];
-    ct_end[r] = fi.res_base + (last ? totals[f].res : table[4 * (r + 1) + 2]);
+    const uint64_t b = fi.res_base + table[4 * r + 2];
+    const uint64_t e = fi.res_base + (last ? totals[f].res : table[4 * (r + 1) + 2]);
+    ct_begin[r] = b;
+    // a contig with len <= k yields nothing (kmers.py:110-117) -- not even the one window of len == k,
+    // and pdg_add_contigs drops it: keep it in the table (rows stay aligned) but empty
+    ct_end[r] = e - b > (uint64_t)k ? e : b;
 }
 
 // ---- host -----------------------------------------------------------------------------------------
@@ -516,7 +520,7 @@ static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint
             const unsigned grid = (unsigned)((rows + 127) / 128);
             fb_hash_kernel<<<grid, 128, 0, s>>>(d_files, gr.f0, gr.f1, d_tot, row_begin, n_rows, d_table);
             PDG_LAUNCHED(g);
-            fb_contigs_kernel<<<grid, 128, 0, s>>>(d_files, gr.f0, gr.f1, d_tot, row_begin, n_rows, d_table, ct_begin, ct_end);
+            fb_contigs_kernel<<<grid, 128, 0, s>>>(d_files, gr.f0, gr.f1, d_tot, row_begin, n_rows, d_table, k, ct_begin, ct_end);
             PDG_LAUNCHED(g);
         }
         if (n_res > res_begin && rows) {
@@ -550,7 +554,7 @@ static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint
     PDG_CUDA(cudaStreamWaitEvent(g->aux_stream, g->i_events[5], 0));
     if (n_rows)
         PDG_CUDA(cudaMemcpyAsync(h_table, d_table, n_rows * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost, g->aux_stream));
-    if (!g->m3_groups.empty()) msd3_finish_launch(g);
+    if (!g->m3_groups.empty()) msd3_finish_launch(g, /*rows=*/2 * k <= kMsd3MaxBits);
     PDG_CUDA(cudaStreamSynchronize(g->aux_stream));
     // the contigs this build assumed (host copy, checked by pdg_finalize)
     g->pre_begin.clear();
@@ -623,7 +627,8 @@ int ingest_fasta_batch(pdg_graph *g, const uint8_t *const *ptrs, const uint64_t 
         getenv("PDG_FB_GROUP_BYTES") ? (uint64_t)atoll(getenv("PDG_FB_GROUP_BYTES")) : FB_GROUP_BYTES;
     static const bool no_pipeline = getenv("PDG_NO_PIPELINE") != nullptr;
     g->pre_valid = false;
-    if (!no_pipeline && 2 * g->k <= kMsd3MaxBits && g->n_res == 0 && g->c_begin.empty() &&
+    // k <= 11: msd3.cu on the whole code; k >= 17: msd3.cu on the 11-residue prefix (msdlong.cu finishes the buckets)
+    if (!no_pipeline && (2 * g->k <= kMsd3MaxBits || g->k > 16) && g->n_res == 0 && g->c_begin.empty() &&
         g->x_src.empty() && g->x_nodes.empty() && tiles) {
         // device images are one group: nothing to overlap but the caller's own bookkeeping
         const int rc = ingest_pipelined(g, ptrs, n_bytes, n_files, h_table, cap_headers, infos, hf, dev, tiles,

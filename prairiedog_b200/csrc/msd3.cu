@@ -509,6 +509,7 @@ void msd3_finish_launch(pdg_graph *g, bool rows) {
         PDG_CUDA(cudaEventRecord(g->k_events[5], s));
     // sentinel: rowtab[n_codes] = number of records (= base of the cell past the last)
     PDG_CUDA(cudaMemcpyAsync(rowtab + n_codes, base32 + cells, 4, cudaMemcpyDeviceToDevice, s));
+    g->m3_launched = true;
     if (!rows) return;   // k > 11 (msdlong.cu): the buckets of the 11-residue prefix are finished there
     // rows: presence -> rank
     uint32_t *flags = g->recA.as<uint32_t>(), *rank = g->scratch1.as<uint32_t>();

@@ -239,7 +239,8 @@ __global__ void __launch_bounds__(ML_BIG_THREADS) ml_big_bucket_kernel(const uns
 
 // true: *sorted (= g->recA) holds the n records {code lo, code hi, position, 0} in (code, position) order and
 // *head_flags (= g->recB) one word per record: 1 where a row (a new code) starts
-bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, const uint4 **sorted,
+// staged: a pipelined ingest already ran the prefix sort up to pass 2 (or 3) for exactly these contigs.
+bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, bool staged, const uint4 **sorted,
                    const uint32_t **head_flags) {
     cudaStream_t s = g->stream;
     const int k = g->k;
@@ -247,10 +248,13 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, c
     const uint32_t n_buckets = 1u << kMsd3MaxBits;
     static const bool off = getenv("PDG_NO_MSDLONG") != nullptr;
     if (off || 2 * k <= kMsd3MaxBits || n == 0 || n >= (1ULL << 32)) return false;
-    g->recA.reserve(n * 16, s);            // before the staging so that nothing is reallocated under it
-    msd3_reserve(g, hc.pos0, hc.pos1, 1);
-    msd3_stage_group(g, ct, hc.pos0, hc.pos1);
-    msd3_finish_launch(g, /*rows=*/false);   // g_pos grouped by prefix, scratch0 = bucket starts (+ sentinel)
+    if (!staged) {
+        g->recA.reserve(n * 16, s);        // before the staging so that nothing is reallocated under it
+        msd3_reserve(g, hc.pos0, hc.pos1, 1);
+        msd3_stage_group(g, ct, hc.pos0, hc.pos1);
+    }
+    if (!g->m3_launched) msd3_finish_launch(g, /*rows=*/false);   // g_pos grouped by prefix, scratch0 = bucket starts (+ sentinel)
+    if (staged) g->recA.reserve(n * 16, s);   // pass 3 no longer reads recA; reserve() drains the stream before it frees
     const uint32_t big_cap = 1u << 18;
     g->ml_flag.reserve(16 + (size_t)big_cap * sizeof(uint2), s);
     PDG_CUDA(cudaMemsetAsync(g->ml_flag.p, 0, 16, s));
@@ -294,10 +298,11 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, c
     PDG_CUDA(cudaStreamSynchronize(s));
     if (getenv("PDG_ML_DEBUG")) fprintf(stderr, "msdlong: %u buckets > %d records, %u > %d\n", h_ctl[1], 512, h_ctl[2], ML_MID);
     const unsigned int h_flag = h_ctl[0];
+    const uint64_t n_groups = g->m3_groups.size();
     g->m3_groups.clear();
     g->m3_launched = false;
     if (h_flag) return false;
-    if (g->m3_timed) {
+    if (g->m3_timed && !staged) {
         float ms[5] = {0, 0, 0, 0, 0}, msw = 0.f;
         for (int i = 0; i < 5; ++i) cudaEventElapsedTime(&ms[i], g->k_events[i], g->k_events[i + 1]);
         cudaEventElapsedTime(&msw, g->k_events[6], g->k_events[7]);
@@ -311,7 +316,7 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, c
     }
     g->stats.sort_passes = 4;
     g->stats.sort_records = n;
-    g->stats.sort_groups = 1;
+    g->stats.sort_groups = n_groups;
     *sorted = out;
     *head_flags = heads;
     return true;

@@ -222,10 +222,12 @@ def _pipelined_worker(group_bytes, k, n_genomes, n_bases, n_contigs, out):
         f.write("%d %d %d %d %d" % (ok, ok2, st["pipelined"], st["sort_groups"], sum(counts)))
 
 
-@pytest.mark.parametrize("group_bytes,k", [(60_000, 11), (250_000, 11), (60_000, 7), (1 << 25, 11), (100_000, 4)])
+@pytest.mark.parametrize("group_bytes,k", [(60_000, 11), (250_000, 11), (60_000, 7), (1 << 25, 11), (100_000, 4),
+                                           (60_000, 21), (250_000, 31), (1 << 25, 17)])
 def test_pipelined_build_equals_oracle(tmp_path, group_bytes, k):
-    """host images, k <= 11, empty graph: passes 1-2 run per copy group inside the ingest call, pass 3 in
-    pdg_finalize; small groups force many groups (and groups smaller than a tile)"""
+    """host images, k <= 11 or k >= 17, empty graph: passes 1-2 run per copy group inside the ingest call and
+    pass 3 is launched at its end; small groups force many groups (and groups smaller than a tile).  For
+    k >= 17 the staged sort is the one on the 11-residue prefix and pdg_finalize finishes the buckets."""
     import torch.multiprocessing as mp
     out = str(tmp_path / "r.txt")
     ctx = mp.get_context("spawn")
@@ -264,3 +266,31 @@ def test_pipelined_build_falls_back_when_contigs_differ():
         o.add_fasta_bytes(i)
     o.build()
     assert e.counts() == o.counts() and e.checksum() == o.checksum()
+
+
+@pytest.mark.parametrize("host", [False, True], ids=["device", "host"])
+@pytest.mark.parametrize("k", [4, 11])
+def test_batch_with_contigs_of_length_k_and_shorter(host, k):
+    """a middle contig of exactly k residues has one window but yields nothing in the reference
+    (kmers.py:110-117: len <= k is skipped); the speculative build of the batch path must agree with
+    the per-file path, which only sees the declared contigs"""
+    from prairiedog_b200 import B200Graph
+    rng = np.random.default_rng(k)
+
+    def seq(n):
+        return bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=n))
+    a = b">a1\n" + seq(60) + b"\n>a_len_k\n" + seq(k) + b"\n>a3\n" + seq(45) + b"\n"
+    b = b">b1\n" + seq(70) + b"\n>b_short\n" + seq(k - 1) + b"\n>b3\n" + seq(k + 1) + b"\n"
+    imgs = [("a.fasta", np.frombuffer(a, dtype=np.uint8)), ("b.fasta", np.frombuffer(b, dtype=np.uint8))]
+    g1 = B200Graph(k=k)
+    for name, img in imgs:
+        g1.add_fasta_bytes(name, img)
+    g1.save()
+    g2 = B200Graph(k=k)
+    counts = g2.add_fasta_batch([(name, img, None if host else g2.engine.to_device(img)) for name, img in imgs])
+    g2.save()
+    assert counts == [60 - k + 1 + 45 - k + 1, 70 - k + 1 + 2]
+    assert g2.engine.counts() == g1.engine.counts()
+    assert g2.engine.counts()[2] == sum(counts)
+    assert g2.canonical() == g1.canonical()
+    assert g2.engine.checksum() == g1.engine.checksum()
