@@ -1,30 +1,36 @@
-"""Node value type and sequence reconstruction -- API mirror of prairiedog/node.py:6-37."""
+"""Node value type of the Graph plugin API and the path -> sequence rule.
+
+Same constructor, attributes and text form as the reference's Node / concat_values
+(prairiedog/node.py:3-37).
+"""
 import typing
 
-DEFAULT_NODE_TYPE = 'km'
+DEFAULT_NODE_TYPE = 'km'          # prairiedog/node.py:3
+_FIELDS = ("value", "node_type", "db_id", "labels")
 
 
-class Node:
-    """A graph node: ``value`` is the k-mer string (prairiedog/node.py:6-16)."""
+class Node(object):
+    """``value`` is the k-mer string (or any other node value of the per-edge API), ``db_id`` the
+    backend's numeric id, ``labels`` extra properties."""
+    __slots__ = _FIELDS
 
-    def __init__(self, value: str, node_type: str = DEFAULT_NODE_TYPE,
-                 db_id: int = None, labels: dict = None):
-        self.value = value
-        self.node_type = node_type
-        self.db_id = db_id
-        self.labels = labels
+    def __init__(self, value: str, node_type: str = DEFAULT_NODE_TYPE, db_id: int = None, labels: dict = None):
+        self.value, self.node_type, self.db_id, self.labels = value, node_type, db_id, labels
+
+    def as_dict(self) -> dict:
+        return {f: getattr(self, f) for f in _FIELDS}
 
     def __str__(self):
-        return "prairiedog.node.Node with vars {}".format(vars(self))
+        return "prairiedog.node.Node with vars {}".format(self.as_dict())
+
+    __repr__ = __str__
 
 
 def concat_values(nodes: typing.Sequence[Node], additional: int = 1) -> str:
-    """Rebuilds the sequence spelled by a node path: the first value plus the last ``additional``
-    characters of every following value (prairiedog/node.py:22-37)."""
-    if len(nodes) == 0:
+    """The sequence a node path spells: consecutive k-mers overlap in all but ``additional`` characters,
+    so it is the first value followed by the tail of every later one (prairiedog/node.py:22-37;
+    "ABC", "BCD" -> "ABCD")."""
+    if not nodes:
         return ""
-    parts = [nodes[0].value]
-    for node in nodes[1:]:
-        v = node.value
-        parts.append(v[len(v) - additional:])
-    return "".join(parts)
+    head, rest = nodes[0].value, nodes[1:]
+    return head + "".join(n.value[len(n.value) - additional:] for n in rest)
