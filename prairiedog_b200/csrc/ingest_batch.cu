@@ -435,6 +435,7 @@ static int ingest_pipelined(pdg_graph *g, const uint8_t *const *ptrs, const uint
         total_bytes += bytes;
         f0 = f1;
     }
+    // (also tried: a last group of a single file -- 14.26 vs 13.94 ms; a group's fixed cost again)
     const uint32_t G = (uint32_t)groups.size();
     // ---- every buffer up front (a reallocation in the middle would stall the pipeline) ----
     const uint64_t words = (total_bytes + 31) / 32 + 2;          // residues <= bytes
