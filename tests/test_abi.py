@@ -115,3 +115,10 @@ def test_layout_follows_reference_loader():
     assert not lay.benign(4)          # two adjacent short contigs
     lay = fasta.Layout(np.array([(0, 2, 0), (9, 11, 6), (14, 16, 8)], dtype=np.uint64), 15)
     assert lay.benign(4) and lay.seq_len.tolist() == [6, 2, 7]
+
+
+def test_integration_doc_names_every_entry_point():
+    """INTEGRATION.md maps every exported symbol to the reference interface it replaces"""
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    missing = [n for n in header_symbols() if "`%s`" % n not in doc]
+    assert missing == []
