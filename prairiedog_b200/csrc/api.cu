@@ -202,6 +202,12 @@ int pdg_snapshot_export(pdg_graph *g, uint64_t *h_words, uint64_t cap_words, uin
                         int32_t *h_value, uint64_t *h_node_code) {
     PDG_API_BEGIN
     const uint64_t words = (g->n_res + 31) / 32;
+    if ((words && !h_words) || (!g->c_begin.empty() && (!h_begin || !h_len || !h_type_id)) ||
+        (!g->x_src.empty() && (!h_src_code || !h_tgt_code || !h_edge_type_id || !h_value)) ||
+        (!g->x_nodes.empty() && !h_node_code)) {
+        set_error("pdg_snapshot_export: null output for a non-empty part (sizes from pdg_snapshot_sizes)");
+        return PDG_E_INVALID;
+    }
     if (words > cap_words) {
         set_error("pdg_snapshot_export: %llu words, capacity %llu", (unsigned long long)words,
                   (unsigned long long)cap_words);
@@ -228,6 +234,14 @@ int pdg_store_import(pdg_graph *g, const uint64_t *h_words, uint64_t n_residues)
     if (g->n_res || !g->c_begin.empty()) {
         set_error("pdg_store_import: the graph already holds %llu residues (pdg_clear first)",
                   (unsigned long long)g->n_res);
+        return PDG_E_INVALID;
+    }
+    if (n_residues && !h_words) {
+        set_error("pdg_store_import: null store");
+        return PDG_E_INVALID;
+    }
+    if (n_residues >= (1ULL << 32)) {
+        set_error("pdg_store_import: %llu residues exceed the 32-bit position column", (unsigned long long)n_residues);
         return PDG_E_INVALID;
     }
     g->pre_valid = false;
