@@ -255,6 +255,7 @@ def run_b200(a):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    bound = distributed.bind_host_to_device(local)      # NUMA-local pinned buffers: one process per GPU
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
@@ -341,6 +342,7 @@ def run_b200(a):
                            "pdg_counts + header table read back; copies overlap the parse inside the library"},
             "gpu_launches": int(st["kernel_launches"]) * a.steps,
             "clocks": clocks,
+            "host_binding": {"cpus_bound_rank0": bound, "how": "NVML CPU affinity of the rank's GPU"},
             "roofline": roof,
             "result": {"n_nodes": int(out[0]), "n_edges_rank0": int(out[1]), "n_kmers_rank0": int(out[2]),
                        "checksums_rank0": [int(x) for x in sums],

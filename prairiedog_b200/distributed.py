@@ -8,6 +8,7 @@ conventions the CUDA side (csrc/comm.cu) relies on:
                  label belongs to one genome, so edges never move between ranks);
 * ``owner``      the rank that deduplicates a node key: the key space is cut into ``world`` equal
                  ranges (csrc/comm.cu:range_owner), so the owned sets concatenate to the sorted table;
+* ``bind_host_to_device``  pins the process to the CPUs local to its GPU before pinned buffers are allocated;
 * ``attach``     hands every rank the same 128-byte NCCL id through ``torch.distributed`` (NCCL on
                  the GPU box, gloo in the CPU tests) and opens the library's communicator;
 * ``reduce_counts``  whole-job edge / k-mer counts (nodes are already global after ``save()``).
@@ -63,6 +64,34 @@ def broadcast_bytes(buf, src=0, device=None):
         t = t.to(device)
     dist.broadcast(t, src)
     return t.cpu().numpy()
+
+
+def bind_host_to_device(index):
+    """Restricts this process to the CPUs that are local to GPU ``index`` (NVML's affinity mask), so that
+    pinned host buffers allocated afterwards land on the GPU's NUMA node (first touch) and host-to-device
+    copies do not cross the socket link.  One process per GPU is the deployment model (torchrun), so this
+    is the process-level analogue of `numactl --cpunodebind`.  Best effort: returns the number of CPUs
+    bound to, or 0 when NVML is unavailable or the mask is empty / outside the allowed set."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        phys = index
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [x.strip() for x in vis.split(",") if x.strip()]
+            if index < len(ids) and ids[index].isdigit():
+                phys = int(ids[index])
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, ((os.cpu_count() or 1) + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if not cpus:
+            return 0
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return 0
 
 
 def attach(graph, device=None):
