@@ -113,3 +113,14 @@ def test_world_size_2_gloo(tmp_path):
     port = _free_port()
     mp.spawn(_worker, args=(2, port, 11, str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok").exists()
+
+
+def test_bind_host_to_device_is_best_effort():
+    """without NVML (this container) nothing is bound and nothing raises; the affinity stays as it was"""
+    import os
+    from prairiedog_b200 import distributed as D
+    before = os.sched_getaffinity(0)
+    n = D.bind_host_to_device(0)
+    assert n == 0 or n == len(os.sched_getaffinity(0))
+    if n == 0:
+        assert os.sched_getaffinity(0) == before
