@@ -139,8 +139,17 @@ __device__ __forceinline__ void m3_partition_tile(M3Smem &sm, RecFn rec, uint32_
             const uint32_t cur = sm.cursor[b];
             sm.delta[b] = cur - run;
             sm.cursor[b] = cur + tot[i];
+#ifdef M3_REREAD_COUNTS
+            // variant for tools/tune_msd3.py ("reread"): read the per-warp counts again instead of keeping them
+            // in registers across the scan (passes 2-3 spill them: 32 / 40 B of stack at 48 registers).
+            // Measured on B200 at 5e8 records, passes 1 / 2 / 3: 2.19 / 2.39 / 2.79 ms against 2.15 / 2.25 / 2.88
+            // -- helps pass 3 only, so it stays off until the choice is per pass.
+#pragma unroll
+            for (int ww = 0; ww < M3_WARPS; ++ww) { const uint32_t cw = sm.wcnt[ww][b]; sm.wcnt[ww][b] = run; run += cw; }
+#else
 #pragma unroll
             for (int ww = 0; ww < M3_WARPS; ++ww) { sm.wcnt[ww][b] = run; run += c[i][ww]; }
+#endif
         }
     }
     __syncthreads();

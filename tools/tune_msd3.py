@@ -9,7 +9,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {"t256i16b3": (256, 16, 3), "t256i16b4": (256, 16, 4), "t512i8b2": (512, 8, 2), "t512i8b3": (512, 8, 3),
             "t256i8b5": (256, 8, 5), "t512i16b1": (512, 16, 1), "t1024i8b1": (1024, 8, 1), "t128i16b6": (128, 16, 6),
-            "cu1": (256, 8, 5, "-DM3_COUNT_UNROLL=1"), "cu2": (256, 8, 5, "-DM3_COUNT_UNROLL=2"), "cu8": (256, 8, 5, "-DM3_COUNT_UNROLL=8")}
+            "cu1": (256, 8, 5, "-DM3_COUNT_UNROLL=1"), "cu2": (256, 8, 5, "-DM3_COUNT_UNROLL=2"), "cu8": (256, 8, 5, "-DM3_COUNT_UNROLL=8"),
+            "reread": (256, 8, 5, "-DM3_REREAD_COUNTS")}
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
 
 
