@@ -33,23 +33,50 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--genomes", type=int, default=100, help="genomes per GPU (config 3: 100)")
+    ap.add_argument("--config", type=int, default=3, choices=[3, 4],
+                    help="BASELINE.json config: 3 = 100 genomes per GPU, k=11, weak scaling (default); 4 = 1000 genomes "
+                         "in total, k=31, ceil(1000/N) per rank, strong scaling (N = 2, 4, 8: one GPU's 32-bit position "
+                         "column holds 4.29e9 residues, the whole job has 5e9)")
+    ap.add_argument("--genomes", type=int, default=None, help="genomes per GPU (config 3: 100) / in total (config 4: 1000)")
     ap.add_argument("--bases", type=int, default=5_000_000)
     ap.add_argument("--contigs", type=int, default=200)
-    ap.add_argument("--k", type=int, default=11)
+    ap.add_argument("--k", type=int, default=None, help="default: 11 (config 3), 31 (config 4)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-sample-bases", type=int, default=1_500_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--iid", action="store_true",
                     help="every genome independent i.i.d. random (worst case for deduplication, SURVEY.md 8d) instead of "
                          "substitutions / indels of one base genome")
-    return ap.parse_args()
+    ap.add_argument("--no-h2d-ceiling", action="store_true", help="skip the copy-only measurement (e2e.h2d_ceiling_gbs)")
+    a = ap.parse_args()
+    if a.k is None:
+        a.k = 31 if a.config == 4 else 11
+    if a.genomes is None:
+        a.genomes = 1000 if a.config == 4 else 100
+    return a
 
 
-def workload_config(a):
+def rank_block(a, rank, world):
+    """(first genome, number of genomes) of a rank: config 3 gives every rank its own `genomes` (weak scaling),
+    config 4 cuts `genomes` into world blocks of ceil(genomes / world) (strong scaling)."""
+    if a.config == 4:
+        per = -(-a.genomes // world)
+        first = min(rank * per, a.genomes)
+        return first, min(per, a.genomes - first)
+    return rank * a.genomes, a.genomes
+
+
+def workload_config(a, world=1):
+    kind = "independent i.i.d. random" if a.iid else "E. coli-like"
+    if a.config == 4:
+        per = -(-a.genomes // world)
+        return {"workload": "config4: %d synthetic %s genomes in total (%.1f Mbp, %d contigs each), k=%d, one pangenome, "
+                            "%d genomes per GPU" % (a.genomes, kind, a.bases / 1e6, a.contigs, a.k, per),
+                "genomes_total": a.genomes, "genomes_per_gpu": per, "bases_per_genome": a.bases,
+                "contigs_per_genome": a.contigs, "k": a.k,
+                "l2": "inputs (%.0f MB of FASTA per GPU and step) exceed the 126 MB L2" % (per * a.bases * 1.0127 / 1e6)}
     return {"workload": "config3: %d synthetic %s genomes per GPU (%.1f Mbp, %d contigs each), k=%d, "
-                        "one pangenome" % (a.genomes, "independent i.i.d. random" if a.iid else "E. coli-like", a.bases / 1e6,
-                                           a.contigs, a.k),
+                        "one pangenome" % (a.genomes, kind, a.bases / 1e6, a.contigs, a.k),
             "genomes_per_gpu": a.genomes, "bases_per_genome": a.bases, "contigs_per_genome": a.contigs, "k": a.k,
             "l2": "inputs (%.0f MB of FASTA per step) exceed the 126 MB L2" % (a.genomes * a.bases * 1.0127 / 1e6)}
 
@@ -141,9 +168,74 @@ def run_reference(a):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": 1e3 * sum(t for _, t in timed) / len(timed),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": workload_config(a), "cpu_baseline": r,
+            "config": dict(workload_config(a, a.gpus), sample_bases=int(a.cpu_sample_bases),
+                           note="every step of this arm is a %d bp SAMPLE of the workload, not the whole of it"
+                                % a.cpu_sample_bases),
+            "cpu_baseline": r,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+# ------------------------------------------------------------------ algorithmic CPU baseline (the C port)
+def cpu_port(a, genomes_1t=20, genomes_par=6):
+    """oracle/pdg_oracle.c (load + sliding window + sort + dedup: the same graph, built the way a CPU would build it
+    in bulk) on a bounded sample of the same genomes: one thread, then one process per host core (independent graphs,
+    an upper bound for a sharded CPU build).  Genome generation is outside the timed region (oracle/port_bench.py)."""
+    def run(first, count):
+        out = subprocess.run([sys.executable, "-m", "oracle.port_bench", str(first), str(count), str(a.k), str(a.bases),
+                              str(a.contigs), "0" if a.iid else "1"], cwd=ROOT, capture_output=True, text=True, timeout=900)
+        return json.loads(out.stdout.strip().splitlines()[-1])
+    one = run(0, genomes_1t)
+    procs = max(1, min(os.cpu_count() or 1, 32))
+    t0 = time.time()
+    jobs = [subprocess.Popen([sys.executable, "-m", "oracle.port_bench", str(i * genomes_par), str(genomes_par), str(a.k),
+                              str(a.bases), str(a.contigs), "0" if a.iid else "1"], cwd=ROOT, stdout=subprocess.PIPE,
+                             text=True) for i in range(procs)]
+    outs = [json.loads(j.communicate(timeout=900)[0].strip().splitlines()[-1]) for j in jobs]
+    # the processes start together; the rate is all bases over the slowest process's timed region
+    par_s = max(o["seconds"] for o in outs)
+    return {"kind": "port", "what": "oracle/pdg_oracle.c, the sort-based C restatement of the path",
+            "one_thread": {"value": one["bases"] / one["seconds"], "unit": UNIT, "cores": 1,
+                           "sample": "%d genomes = %d bp in %.2f s" % (genomes_1t, one["bases"], one["seconds"])},
+            "all_cores": {"value": sum(o["bases"] for o in outs) / par_s, "unit": UNIT, "cores": procs,
+                          "sample": "%d processes x %d genomes = %d bp, slowest process %.2f s (independent graphs: an "
+                                    "upper bound for a sharded CPU build, not one pangenome)"
+                                    % (procs, genomes_par, sum(o["bases"] for o in outs), par_s)}}
+
+
+# ------------------------------------------------------------------ parity gate
+GOLDEN = os.path.join(ROOT, "tests", "golden", "bench_checksums.json")
+
+
+def parity_verdict(a, world, n_nodes, nodes_sum, per_rank):
+    """Compares what the timed graph holds with tests/golden/bench_checksums.json (written from oracle/pdg_oracle.c
+    by tests/golden/make_bench_checksums.py).  per_rank: [(n_edges, n_kmers, edges_sum)] in rank order.
+    Returns {"parity": "ok" | "MISMATCH" | "unchecked", ...}."""
+    standard = (a.bases == 5_000_000 and a.contigs == 200 and not a.iid and a.k in (11, 31))
+    if not standard or not os.path.exists(GOLDEN):
+        return {"parity": "unchecked", "why": "no golden values for this shape" if standard or os.path.exists(GOLDEN)
+                else "tests/golden/bench_checksums.json missing"}
+    gold = json.load(open(GOLDEN))
+    if a.config == 4 and a.genomes == 1000 and a.k == 31:
+        bkey, nkey = "config4_n%d_k31" % world, "first_1000_k31"
+    elif a.config == 3 and a.genomes == 100:
+        bkey, nkey = "weak_k%d" % a.k, "first_%d_k%d" % (100 * world, a.k)
+    else:
+        return {"parity": "unchecked", "why": "no golden values for this shape"}
+    blocks, nodes = gold["blocks"].get(bkey), gold["nodes"].get(nkey)
+    if blocks is None or nodes is None or len(blocks) < world:
+        return {"parity": "unchecked", "why": "golden file has no %s / %s" % (bkey, nkey)}
+    bad = []
+    if (int(n_nodes), int(nodes_sum)) != (nodes["n_nodes"], nodes["nodes_sum"]):
+        bad.append("nodes: got (%d, %d) want (%d, %d)" % (n_nodes, nodes_sum, nodes["n_nodes"], nodes["nodes_sum"]))
+    for r, (ne, nk, es) in enumerate(per_rank):
+        b = blocks[r]
+        if (int(ne), int(nk), int(es)) != (b["n_edges"], b["n_kmers"], b["edges_sum"]):
+            bad.append("rank %d edges: got (%d, %d, %d) want (%d, %d, %d)" % (r, ne, nk, es, b["n_edges"], b["n_kmers"],
+                                                                              b["edges_sum"]))
+    return {"parity": "MISMATCH" if bad else "ok", "golden": "tests/golden/bench_checksums.json [%s, %s]" % (bkey, nkey),
+            "checked": "global node count + node checksum; per rank edge count, k-mer count, edge checksum (%d ranks)" % world,
+            **({"mismatches": bad} if bad else {})}
 
 
 # ------------------------------------------------------------------ clocks
@@ -264,8 +356,12 @@ def run_b200(a):
     distributed.attach(g, dev)          # N > 1: every rank gets the NCCL id, opens the communicator
 
     # synthetic genomes of this rank: pinned host images and device-resident copies
+    first, count = rank_block(a, rank, world)
+    if count * a.bases >= (1 << 32):
+        raise SystemExit("bench.py: %d genomes x %d bp on one GPU exceed the 32-bit position column of the occurrence "
+                         "index (4.29e9 residues per GPU); config 4 runs on 2, 4 or 8 GPUs" % (count, a.bases))
     files, n_bases = [], 0
-    for name, buf, lens in synth.genomes(a.genomes, n_bases=a.bases, n_contigs=a.contigs, first=rank * a.genomes, related=not a.iid):
+    for name, buf, lens in synth.genomes(count, n_bases=a.bases, n_contigs=a.contigs, first=first, related=not a.iid):
         pinned = torch.from_numpy(buf).pin_memory()
         files.append((name, pinned.numpy(), pinned.to(dev), pinned))
         n_bases += int(lens.sum())
@@ -308,11 +404,44 @@ def run_b200(a):
     st = g.engine.stats()
     ms_e2e, out_e2e, _ = timed(False, a.steps, a.warmup)
     st_e2e = g.engine.stats()
-    sums = g.engine.checksum()       # canonical node / edge set checksums of the e2e graph (outside the timed region)
-    total_bases = torch.tensor([float(n_bases)], device=dev, dtype=torch.float64)
+    # ---- parity gate (outside the timed region): checksums of the graph the last e2e step built, every rank's ----
+    sums = g.engine.checksum()       # collective when world > 1: gathers the global node table on every rank
+    mine = torch.tensor([int(out_e2e[1]), int(out_e2e[2]), int(sums[1]) & 0xffffffff, int(sums[1]) >> 32, bound],
+                        device=dev, dtype=torch.int64)
+    gathered = [torch.zeros_like(mine) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(gathered, mine)
+    else:
+        gathered = [mine]
+    per_rank = [(int(t[0]), int(t[1]), int(t[2]) | (int(t[3]) << 32)) for t in gathered]
+    bound_all = [int(t[4]) for t in gathered]
+    verdict = parity_verdict(a, world, int(out_e2e[0]), int(sums[0]), per_rank)
+
+    # ---- what the node can deliver: every rank copies its pinned images to the device at once, no compute ----
+    ceiling = None
+    if not a.no_h2d_ceiling:
+        for f in files:
+            f[2].copy_(f[3], non_blocking=True)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 3
+        c0.record()
+        for _ in range(reps):
+            for f in files:
+                f[2].copy_(f[3], non_blocking=True)
+        c1.record()
+        torch.cuda.synchronize()
+        cms = torch.tensor([c0.elapsed_time(c1) / reps], device=dev)
+        if world > 1:
+            dist.all_reduce(cms, op=dist.ReduceOp.MAX)
+        ceiling = float(cms.item())
+    total_bases = torch.tensor([float(n_bases), float(h2d_bytes)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(total_bases)
-    total_bases = float(total_bases.item())
+    total_h2d = float(total_bases[1].item())
+    total_bases = float(total_bases[0].item())
 
     if rank == 0:
         peaks = {}
@@ -334,19 +463,25 @@ def run_b200(a):
                            "profiles/ x units", "all_kernels": kernels}
         line = {
             "metric": METRIC, "value": total_bases / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": a.steps,
-            "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u64", "data": "synthetic", "config": workload_config(a),
+            "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "strong" if a.config == 4 else "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic", "config": workload_config(a, world),
             "e2e": {"value": total_bases / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 5 * 8 + int(st["n_contigs"]) * 32 + 48 * len(files), "ms_per_step": ms_e2e,
                     "how": "pinned host FASTA images -> pdg_ingest_fasta_batch(PDG_IN_HOST) -> pdg_finalize -> "
-                           "pdg_counts + header table read back; copies overlap the parse inside the library"},
+                           "pdg_counts + header table read back; copies overlap the parse inside the library",
+                    # the same pinned buffers copied by all ranks at once with NO compute: the node's host->device
+                    # ceiling for this job (max over ranks), against which e2e scaling has to be read
+                    "h2d_ceiling_ms": ceiling,
+                    "h2d_ceiling_gbs": (total_h2d / (ceiling * 1e-3) / 1e9) if ceiling else None,
+                    "h2d_ceiling_gbs_per_gpu": (total_h2d / world / (ceiling * 1e-3) / 1e9) if ceiling else None},
             "gpu_launches": int(st["kernel_launches"]) * a.steps,
             "clocks": clocks,
-            "host_binding": {"cpus_bound_rank0": bound, "how": "NVML CPU affinity of the rank's GPU"},
+            "host_binding": {"cpus_bound_per_rank": bound_all, "how": "NVML CPU affinity of the rank's GPU (0 = not bound)"},
             "roofline": roof,
-            "result": {"n_nodes": int(out[0]), "n_edges_rank0": int(out[1]), "n_kmers_rank0": int(out[2]),
-                       "checksums_rank0": [int(x) for x in sums],
-                       "e2e_counts_equal_resident": list(out_e2e) == list(out)},
+            "result": dict(verdict, n_nodes=int(out_e2e[0]), nodes_sum=int(sums[0]),
+                           per_rank=[{"n_edges": e, "n_kmers": k_, "edges_sum": s_} for e, k_, s_ in per_rank],
+                           e2e_counts_equal_resident=list(out_e2e) == list(out)),
             "phases_ms": dict([(k, st[k]) for k in ("ms_upload", "ms_sort", "ms_explicit", "ms_nodes", "ms_total")] +
                               [("ms_ingest_a", st["ms_ingest_a"]), ("ms_ingest_b", st["ms_ingest_b"]),
                                ("ms_ingest_c", st["ms_ingest_c"]),
@@ -356,9 +491,13 @@ def run_b200(a):
         }
         if world == 1 and not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_reference(a, a.cpu_sample_bases)
+            line["cpu_baseline"]["port"] = cpu_port(a)     # the honest algorithmic CPU baseline beside the engine's
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    if verdict["parity"] == "MISMATCH" or list(out_e2e) != list(out):
+        sys.stderr.write("bench.py: PARITY MISMATCH against tests/golden/bench_checksums.json: %s\n" % json.dumps(verdict))
+        raise SystemExit(3)
 
 
 def kernel_table(st, k, peak):

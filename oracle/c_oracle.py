@@ -43,6 +43,18 @@ def lib():
         L.orc_checksum.argtypes = [vp, vp, vp]
         L.orc_query.restype = u64
         L.orc_query.argtypes = [vp, u64, u64, i64, ctypes.c_int, vp, u64]
+        L.orc_stream_sums.argtypes = [vp, vp, ctypes.c_int, vp, vp, vp]
+        L.orc_mark_codes.restype = ctypes.c_int
+        L.orc_mark_codes.argtypes = [vp, vp]
+        L.orc_bitmap_sum.argtypes = [vp, u64, vp, vp]
+        L.orc_emit_codes.restype = u64
+        L.orc_emit_codes.argtypes = [vp, vp]
+        L.orc_sort_unique.restype = u64
+        L.orc_sort_unique.argtypes = [vp, vp, u64, ctypes.c_int]
+        L.orc_merge_unique.restype = u64
+        L.orc_merge_unique.argtypes = [vp, u64, vp, u64, vp]
+        L.orc_codes_sum.restype = u64
+        L.orc_codes_sum.argtypes = [vp, u64]
         _lib = L
     return _lib
 
@@ -115,3 +127,50 @@ class COracle(object):
             if n <= cap:
                 return hits[:n]
             cap = int(n)
+
+    # ---- streaming forms (no occurrence list; inputs too large to sort in one piece) ----
+    def stream_sums(self, type_offsets=(0,)):
+        """(n_kmers, n_edges, [edge checksum with type ids shifted by every offset]) of the loaded contigs."""
+        off = np.ascontiguousarray(type_offsets, dtype=np.uint32)
+        sums = np.zeros(off.size, dtype=np.uint64)
+        nk, ne = ctypes.c_uint64(), ctypes.c_uint64()
+        self.L.orc_stream_sums(self.h, off.ctypes.data, off.size, ctypes.addressof(nk), ctypes.addressof(ne),
+                               sums.ctypes.data)
+        return nk.value, ne.value, [int(x) for x in sums]
+
+    def mark_codes(self, bitmap):
+        """ORs the presence bit of every emitted code into ``bitmap`` (uint64 words, 4^k bits; k <= 15)."""
+        if self.L.orc_mark_codes(self.h, bitmap.ctypes.data) != 0:
+            raise ValueError("orc_mark_codes: k > 15")
+
+    def distinct_codes(self):
+        """Sorted distinct emitted codes of the loaded contigs."""
+        n = self.L.orc_emit_codes(self.h, None)
+        a, t = np.empty(max(n, 1), dtype=np.uint64), np.empty(max(n, 1), dtype=np.uint64)
+        self.L.orc_emit_codes(self.h, a.ctypes.data)
+        m = self.L.orc_sort_unique(a.ctypes.data, t.ctypes.data, n, 2 * self.k)
+        return a[:m].copy()
+
+
+def bitmap_sum(bitmap):
+    n, s = ctypes.c_uint64(), ctypes.c_uint64()
+    lib().orc_bitmap_sum(bitmap.ctypes.data, bitmap.size, ctypes.addressof(n), ctypes.addressof(s))
+    return n.value, s.value
+
+
+def sort_unique(codes, key_bits):
+    """Sorted distinct values of a uint64 array (destroyed)."""
+    t = np.empty(max(codes.size, 1), dtype=np.uint64)
+    m = lib().orc_sort_unique(codes.ctypes.data, t.ctypes.data, codes.size, int(key_bits))
+    return codes[:m]
+
+
+def merge_unique(a, b):
+    out = np.empty(a.size + b.size, dtype=np.uint64)
+    m = lib().orc_merge_unique(a.ctypes.data, a.size, b.ctypes.data, b.size, out.ctypes.data)
+    return out[:m]
+
+
+def codes_sum(codes):
+    codes = np.ascontiguousarray(codes, dtype=np.uint64)
+    return int(lib().orc_codes_sum(codes.ctypes.data, codes.size))

@@ -322,3 +322,122 @@ uint64_t orc_query(const orc_graph *g, uint64_t a, uint64_t b, int64_t max_len, 
     }
     return n;
 }
+
+/* ---- streaming forms for inputs too large to sort in one piece (tests/golden/make_bench_checksums.py) ----
+ * They restate the SAME definitions as orc_build + orc_checksum without materialising the occurrence list;
+ * tests/test_oracle_pinning.py checks them against orc_build / orc_checksum on the fixtures.
+ * Valid for what orc_add_fasta accepts with every contig carrying its own type id (no (type, value) pair can
+ * repeat, so the labelled edge SET of lemongraph.c:661-685 is one edge per non-final k-mer occurrence). */
+
+/* n_off edge sums at once: sums[o] uses type id (contig type + type_off[o]) -- one pass over the residues */
+void orc_stream_sums(const orc_graph *g, const uint32_t *type_off, int n_off, uint64_t *n_kmers, uint64_t *n_edges,
+                     uint64_t *sums) {
+    const int k = g->k;
+    const uint64_t mask = (1ULL << (2 * k)) - 1ULL;
+    uint64_t nk = 0, ne = 0;
+    for (int o = 0; o < n_off; ++o) sums[o] = 0;
+    for (uint64_t c = 0; c < g->n_contigs; ++c) {
+        const orc_contig *ct = &g->contigs[c];
+        if (ct->len <= (uint64_t)k) continue;            /* kmers.py:110-117 */
+        uint64_t code = 0, prev = 0;
+        for (uint64_t p = 0; p < ct->len; ++p) {
+            code = ((code << 2) | g->res[ct->begin + p]) & mask;
+            if (p + 1 < (uint64_t)k) continue;
+            nk++;
+            if (p + 1 > (uint64_t)k) {                   /* edge prev -> code, value = start of prev */
+                const uint64_t val = p - (uint64_t)k;    /* (p + 1 - k) - 1 */
+                const uint64_t h2 = mix64(mix64(prev + 0x9e3779b97f4a7c15ULL) ^ code);
+                for (int o = 0; o < n_off; ++o)
+                    sums[o] += mix64(h2 ^ (((uint64_t)(ct->type + type_off[o]) << 32) | (uint32_t)(int32_t)val));
+                ne++;
+            }
+            prev = code;
+        }
+    }
+    *n_kmers = nk;
+    *n_edges = ne;
+}
+
+/* presence bits of every emitted k-mer code, OR-ed into bitmap (4^k bits, 64 per word); k <= 15 */
+int orc_mark_codes(const orc_graph *g, uint64_t *bitmap) {
+    const int k = g->k;
+    if (k > 15) return -1;
+    const uint64_t mask = (1ULL << (2 * k)) - 1ULL;
+    for (uint64_t c = 0; c < g->n_contigs; ++c) {
+        const orc_contig *ct = &g->contigs[c];
+        if (ct->len <= (uint64_t)k) continue;
+        uint64_t code = 0;
+        for (uint64_t p = 0; p < ct->len; ++p) {
+            code = ((code << 2) | g->res[ct->begin + p]) & mask;
+            if (p + 1 >= (uint64_t)k) bitmap[code >> 6] |= 1ULL << (code & 63);
+        }
+    }
+    return 0;
+}
+
+/* count and node checksum of the codes whose bit is set */
+void orc_bitmap_sum(const uint64_t *bitmap, uint64_t n_words, uint64_t *n_nodes, uint64_t *nodes_sum) {
+    uint64_t n = 0, s = 0;
+    for (uint64_t w = 0; w < n_words; ++w)
+        for (uint64_t m = bitmap[w]; m; m &= m - 1) {
+            const uint64_t code = (w << 6) | (uint64_t)__builtin_ctzll(m);
+            s += mix64(code + 0x9e3779b97f4a7c15ULL);
+            n++;
+        }
+    *n_nodes = n;
+    *nodes_sum = s;
+}
+
+/* every emitted k-mer code of the loaded contigs, in emission order; returns the count (out may be NULL) */
+uint64_t orc_emit_codes(const orc_graph *g, uint64_t *out) {
+    const int k = g->k;
+    const uint64_t mask = (1ULL << (2 * k)) - 1ULL;
+    uint64_t n = 0;
+    for (uint64_t c = 0; c < g->n_contigs; ++c) {
+        const orc_contig *ct = &g->contigs[c];
+        if (ct->len <= (uint64_t)k) continue;
+        uint64_t code = 0;
+        for (uint64_t p = 0; p < ct->len; ++p) {
+            code = ((code << 2) | g->res[ct->begin + p]) & mask;
+            if (p + 1 >= (uint64_t)k) { if (out) out[n] = code; n++; }
+        }
+    }
+    return n;
+}
+
+/* in place: LSD radix sort of n keys on key_bits bits (tmp: n words), then adjacent dedup; returns the count */
+uint64_t orc_sort_unique(uint64_t *a, uint64_t *tmp, uint64_t n, int key_bits) {
+    uint64_t *cnt = (uint64_t *)malloc(2049 * sizeof(uint64_t));
+    uint64_t *src = a, *dst = tmp;
+    for (int shift = 0; shift < key_bits; shift += 11) {
+        memset(cnt, 0, 2049 * sizeof(uint64_t));
+        for (uint64_t i = 0; i < n; ++i) cnt[((src[i] >> shift) & 2047) + 1]++;
+        for (int d = 0; d < 2048; ++d) cnt[d + 1] += cnt[d];
+        for (uint64_t i = 0; i < n; ++i) dst[cnt[(src[i] >> shift) & 2047]++] = src[i];
+        uint64_t *t = src; src = dst; dst = t;
+    }
+    free(cnt);
+    uint64_t m = 0;
+    for (uint64_t i = 0; i < n; ++i)
+        if (i == 0 || src[i] != src[i - 1]) a[m++] = src[i];   /* a == src or a == dst: writes trail reads */
+    return m;
+}
+
+/* union of two sorted duplicate-free arrays into out (room for na + nb); returns the count */
+uint64_t orc_merge_unique(const uint64_t *a, uint64_t na, const uint64_t *b, uint64_t nb, uint64_t *out) {
+    uint64_t i = 0, j = 0, m = 0;
+    while (i < na && j < nb) {
+        if (a[i] < b[j]) out[m++] = a[i++];
+        else if (b[j] < a[i]) out[m++] = b[j++];
+        else { out[m++] = a[i++]; j++; }
+    }
+    while (i < na) out[m++] = a[i++];
+    while (j < nb) out[m++] = b[j++];
+    return m;
+}
+
+uint64_t orc_codes_sum(const uint64_t *codes, uint64_t n) {
+    uint64_t s = 0;
+    for (uint64_t i = 0; i < n; ++i) s += mix64(codes[i] + 0x9e3779b97f4a7c15ULL);
+    return s;
+}
