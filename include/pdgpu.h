@@ -48,7 +48,7 @@
 extern "C" {
 #endif
 
-#define PDG_ABI_VERSION 4
+#define PDG_ABI_VERSION 5
 
 #define PDG_OK            0
 #define PDG_E_INVALID    -1   /* bad argument / bad state */
@@ -189,6 +189,11 @@ int pdg_add_nodes_host(pdg_graph *g, const uint64_t *h_code, uint64_t n);
 #define PDG_F_FORCE_SORT_NODES 1
 #define PDG_F_FORCE_GENERAL    2
 int pdg_finalize(pdg_graph *g, int flags);
+/* Commit semantics: pdg_add_contigs / pdg_add_edges_host / pdg_add_nodes_host / pdg_ingest_fasta* after a
+ * pdg_finalize do NOT invalidate its index -- queries, exports and pdg_counts keep answering from the last finalized
+ * state until the next pdg_finalize, like a LemonGraph read transaction beside an open write transaction
+ * (lemon_graph.py:178-180 vs :54-64).  Before the first pdg_finalize, and after pdg_clear, they fail / report an
+ * empty graph. */
 int pdg_counts(pdg_graph *g, uint64_t *n_nodes, uint64_t *n_edges, uint64_t *n_kmers);
 int pdg_get_build_stats(pdg_graph *g, pdg_build_stats *out);
 
@@ -226,10 +231,25 @@ int pdg_query_paths(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint
 int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits);
 int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_node_codes,
                    int32_t *status);
+/* A query whose hit count does not fit 32 bits fails the whole call with PDG_E_CAPACITY (nothing is written). */
 
-/* K5: multi-GPU (one process per GPU).  The host exchanges the 128-byte id with
- * torch.distributed; node keys are hash partitioned with one grouped ncclSend/ncclRecv exchange
- * inside pdg_finalize.  No reference counterpart. */
+/* The STRING of every hit of the last pdg_query_paths call in one go: Prairiedog.query spells a path with
+ * concat_values (prairiedog/prairiedog.py:22-31, prairiedog/node.py:22-37) = the first node value followed by the
+ * last character of every later one = residues [begin + i, begin + j + 1 + k) of the hit's contig, decoded from the
+ * 2-bit store by one kernel (replaces one pdg_query_walk round trip per hit).
+ * pdg_query_strings_size sizes the byte buffer; pdg_query_strings_fetch fills h_offsets[n_hits + 1] (byte offset of
+ * hit h's string; starts are 16-byte aligned, so the LENGTH is j - i + 1 + k, not the difference of two offsets) and
+ * h_bytes (ASCII, pinned memory recommended).  Hits of the explicit part (aux & PDG_HIT_EXPLICIT) have length 0:
+ * their node values can be opaque host strings, spell them with pdg_query_walk. */
+int pdg_query_strings_size(pdg_graph *g, uint64_t *total_bytes);
+int pdg_query_strings_fetch(pdg_graph *g, uint64_t *h_offsets, uint8_t *h_bytes);
+
+/* K5: multi-GPU (one process per GPU).  The host exchanges the 128-byte id with torch.distributed.  Genomes shard
+ * by sample and edges never move; inside pdg_finalize the ranks agree on the global node table: for k <= 15 one
+ * ncclAllGather of the presence bitmaps + an OR, otherwise the 2k-bit key space is RANGE partitioned into `world`
+ * equal slices (csrc/comm.cu:range_owner) and every rank sends each owner its slice of its sorted table with one
+ * grouped ncclSend/ncclRecv exchange.  pdg_destroy destroys the communicator.  No reference counterpart
+ * (SURVEY.md 2.2). */
 int pdg_comm_unique_id(uint8_t *h_id128);
 int pdg_comm_init(pdg_graph *g, const uint8_t *h_id128, int rank, int world);
 

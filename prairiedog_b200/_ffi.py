@@ -67,6 +67,8 @@ class BuildStats(ctypes.Structure):
                 ("pad3", ctypes.c_float), ("sort_groups", c_u64), ("pipelined", c_u64), ("ingest_bytes", c_u64), ("ingest_launches", c_u64)]
 
 
+ABI_VERSION = 5      # PDG_ABI_VERSION of include/pdgpu.h
+
 # name -> (restype, argtypes); every symbol of include/pdgpu.h (tests/test_abi.py checks the list
 # against the header)
 SIGNATURES = {
@@ -101,6 +103,8 @@ SIGNATURES = {
     "pdg_query_paths": (c_int, [vp, vp, vp, c_u64, c_i64, u64p]),
     "pdg_query_fetch": (c_int, [vp, vp, vp]),
     "pdg_query_walk": (c_int, [vp, c_u64, ctypes.POINTER(Hit), vp, i32p]),
+    "pdg_query_strings_size": (c_int, [vp, u64p]),
+    "pdg_query_strings_fetch": (c_int, [vp, vp, vp]),
     "pdg_comm_unique_id": (c_int, [vp]),
     "pdg_comm_init": (c_int, [vp, vp, c_int, c_int]),
 }
@@ -124,8 +128,8 @@ def load(build_if_missing=False):
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    if lib.pdg_abi_version() != 4:
-        raise PdgError(PDG_E_INVALID, "libpdgpu ABI %d, expected 4: rebuild" % lib.pdg_abi_version())
+    if lib.pdg_abi_version() != ABI_VERSION:
+        raise PdgError(PDG_E_INVALID, "libpdgpu ABI %d, expected %d: rebuild" % (lib.pdg_abi_version(), ABI_VERSION))
     _lib = lib
     return lib
 

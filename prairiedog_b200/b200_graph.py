@@ -18,6 +18,7 @@ import numpy as np
 from . import codec, fasta
 from .edge import Edge
 from .engine import Engine, HIT_EXPLICIT
+from .errors import GraphException
 from .graph import Graph
 from .node import Node, DEFAULT_NODE_TYPE
 
@@ -346,13 +347,15 @@ class B200Graph(Graph):
 
     @staticmethod
     def _dup_headers(host, table):
-        """True when two header lines of the file are byte-identical."""
+        """True when two header lines of the file give the same label.  Labels are the RIGHT-STRIPPED lines
+        (kmers.py:63 `line.rstrip()`), so '>c1' and '>c1 ' are one edge_type; bytes.rstrip() strips the same ASCII
+        whitespace set as the device hash of the batched path (csrc/ingest_batch.cu fb_hash_kernel)."""
         if table.shape[0] < 2:
             return False
         mv = memoryview(host)
         seen = set()
         for b, e in table[:, :2].tolist():
-            seen.add(bytes(mv[b:e]))
+            seen.add(bytes(mv[b:e]).rstrip())
         return len(seen) != table.shape[0]
 
     # ------------------------------------------------------------------ enumeration
@@ -459,29 +462,62 @@ class B200Graph(Graph):
         hit dicts {'string', 'edge_type', 'i', 'j'}; 'string' is concat_values (node.py:22-37) of the
         hit's node chain, spelled from the codes without building Node objects."""
         a, off, hits = self.path_many(pairs, limit)
+        spell = self._hit_strings(a, off, hits) if strings else None
         out = []
+        tid, hi, hj = hits["type_id"].tolist(), hits["i"].tolist(), hits["j"].tolist()
         for q in range(len(pairs)):
             row = []
-            for h in hits[int(off[q]):int(off[q + 1])]:
-                d = {'edge_type': self._type_string(h["type_id"]), 'i': int(h["i"]), 'j': int(h["j"])}
+            for x in range(int(off[q]), int(off[q + 1])):
+                d = {'edge_type': self._type_string(tid[x]), 'i': hi[x], 'j': hj[x]}
                 if strings:
-                    codes, status = self.engine.walk(int(a[q]), h)
-                    assert status == 0, "Length of chains is {} != 1".format(0 if status == 1 else 2)
-                    vals = [self._value(c) for c in codes.tolist()]
-                    d['string'] = vals[0] + ''.join(v[-1] for v in vals[1:])
+                    d['string'] = spell[x]
                 row.append(d)
             out.append(row)
+        return out
+
+    def _hit_strings(self, a, off, hits):
+        """concat_values (node.py:22-37) of every hit of the LAST path_many call: genome-part hits are decoded on
+        the device in one pdg_query_strings call (contig[i : j + 1 + k]); explicit-part hits, whose node values can
+        be opaque host strings, follow their chain with pdg_query_walk (lemon_graph.py:244-264)."""
+        n = int(hits.size)
+        if n == 0:
+            return []
+        soff, sbytes = self.engine.query_strings()
+        raw = sbytes.tobytes()
+        lens = (hits["j"].astype(np.int64) - hits["i"].astype(np.int64) + 1 + self.k).tolist()
+        explicit = ((hits["aux"] & HIT_EXPLICIT) != 0).tolist()
+        soff = soff.tolist()
+        out = [None] * n
+        qof = np.repeat(np.arange(len(off) - 1), np.diff(off.astype(np.int64))).tolist() if any(explicit) else None
+        for x in range(n):
+            if explicit[x]:
+                codes, status = self.engine.walk(int(a[qof[x]]), hits[x])
+                # lemon_graph.py:254-258: exactly one chain must spell the path (an AssertionError there too)
+                assert status == 0, "Length of chains is {} != 1".format(0 if status == 1 else 2)
+                vals = [self._value(c) for c in codes.tolist()]
+                out[x] = vals[0] + ''.join(v[-1] for v in vals[1:])
+            else:
+                out[x] = raw[soff[x]:soff[x] + lens[x]].decode("ascii")
         return out
 
     def path(self, node_a: str, node_b: str) -> typing.Tuple[tuple, tuple]:
         """lemon_graph.py:275-334."""
         a, off, hits = self.path_many([(node_a, node_b)])
         paths, metas = [], []
-        for h in hits:
-            codes, status = self.engine.walk(int(a[0]), h)
-            # lemon_graph.py:254-258: exactly one chain must spell the path
-            assert status == 0, "Length of chains is {} != 1".format(0 if status == 1 else 2)
-            paths.append(tuple(self._make_node(c) for c in codes.tolist()))
+        spell = self._hit_strings(a, off, hits)
+        k = self.k
+        for x, h in enumerate(hits):
+            if int(h["aux"]) & HIT_EXPLICIT:
+                codes, status = self.engine.walk(int(a[0]), h)
+                # lemon_graph.py:254-258: exactly one chain must spell the path (an AssertionError there too)
+                assert status == 0, "Length of chains is {} != 1".format(0 if status == 1 else 2)
+                codes = codes.tolist()
+            else:       # genome part: node t of the path is the k-mer at offset t of the hit's string
+                s = spell[x]
+                codes = [codec.encode(s[t:t + k], k) for t in range(len(s) - k + 1)]
+            if len(codes) < 2:          # lemon_graph.py:315-316
+                raise GraphException(self)
+            paths.append(tuple(self._make_node(c) for c in codes))
             meta = {'edge_type': self._type_string(h["type_id"])}
             lab = self._edge_labels.get((int(codes[0]), int(codes[1]), int(h["type_id"]), int(h["i"])))
             if lab:

@@ -71,6 +71,7 @@ void pdg_destroy(pdg_graph *g) {
     if (!g) return;
     cudaSetDevice(g->device);
     cudaStreamSynchronize(g->stream);
+    comm_destroy(g);
     if (g->ev0) cudaEventDestroy(g->ev0);
     if (g->ev1) cudaEventDestroy(g->ev1);
     if (g->fb_ev_ready) cudaEventDestroy(g->fb_ev_ready);
@@ -161,7 +162,9 @@ int pdg_add_contigs(pdg_graph *g, const uint64_t *h_begin, const uint64_t *h_len
         g->c_type.push_back(h_type_id[i]);
         g->n_kmers += h_len[i] - k + 1;
     }
-    g->finalized = false;
+    // g->finalized stays as it is: declaring contigs only appends to host vectors, the index of the last
+    // pdg_finalize is untouched and keeps answering queries -- LemonGraph's read transactions see the last COMMITTED
+    // state while a write transaction is open (prairiedog/lemon_graph.py:178-180 against :54-64)
     return PDG_OK;
     PDG_API_END
 }
@@ -272,16 +275,14 @@ int pdg_add_edges_host(pdg_graph *g, const uint64_t *h_src_code, const uint64_t 
     g->x_tgt.insert(g->x_tgt.end(), h_tgt_code, h_tgt_code + n);
     g->x_type.insert(g->x_type.end(), h_type_id, h_type_id + n);
     g->x_val.insert(g->x_val.end(), h_value, h_value + n);
-    g->finalized = false;
-    return PDG_OK;
+    return PDG_OK;      // committed index stays valid, see pdg_add_contigs
     PDG_API_END
 }
 
 int pdg_add_nodes_host(pdg_graph *g, const uint64_t *h_code, uint64_t n) {
     PDG_API_BEGIN
     g->x_nodes.insert(g->x_nodes.end(), h_code, h_code + n);
-    g->finalized = false;
-    return PDG_OK;
+    return PDG_OK;      // committed index stays valid, see pdg_add_contigs
     PDG_API_END
 }
 
@@ -295,7 +296,8 @@ int pdg_counts(pdg_graph *g, uint64_t *n_nodes, uint64_t *n_edges, uint64_t *n_k
     PDG_API_BEGIN
     if (n_nodes) *n_nodes = g->n_nodes;
     if (n_edges) *n_edges = g->n_edges;
-    if (n_kmers) *n_kmers = g->n_kmers;
+    // after a pdg_finalize: the k-mers of the committed graph (contigs declared since are not in it yet)
+    if (n_kmers) *n_kmers = g->finalized ? g->stats.n_kmers : g->n_kmers;
     return PDG_OK;
     PDG_API_END
 }
@@ -409,6 +411,22 @@ int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits) {
 int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_node_codes, int32_t *status) {
     PDG_API_BEGIN
     return query_walk(g, src_code, hit, h_node_codes, status);
+    PDG_API_END
+}
+
+int pdg_query_strings_size(pdg_graph *g, uint64_t *total_bytes) {
+    PDG_API_BEGIN
+    if (!total_bytes) {
+        set_error("pdg_query_strings_size: null argument");
+        return PDG_E_INVALID;
+    }
+    return query_strings_size(g, total_bytes);
+    PDG_API_END
+}
+
+int pdg_query_strings_fetch(pdg_graph *g, uint64_t *h_offsets, uint8_t *h_bytes) {
+    PDG_API_BEGIN
+    return query_strings_fetch(g, h_offsets, h_bytes);
     PDG_API_END
 }
 

@@ -299,6 +299,19 @@ int comm_materialize_nodes(pdg_graph *g) {
 
 using namespace pdg;
 
+namespace pdg {
+// pdg_destroy: the communicator belongs to the handle
+void comm_destroy(pdg_graph *g) {
+    if (!g->nccl_comm) return;
+    NcclApi *api = nccl_api();
+    if (api && api->CommDestroy) api->CommDestroy(static_cast<ncclComm_t>(g->nccl_comm));
+    g->nccl_comm = nullptr;
+    g->world = 1;
+    g->rank = 0;
+}
+
+}  // namespace pdg
+
 extern "C" {
 
 int pdg_comm_unique_id(uint8_t *h_id128) {
@@ -333,6 +346,7 @@ int pdg_comm_init(pdg_graph *g, const uint8_t *h_id128, int rank, int world) {
         set_error("ncclCommInitRank failed: %s", api->GetErrorString ? api->GetErrorString(r) : "?");
         return PDG_E_COMM;
     }
+    if (g->nccl_comm && api->CommDestroy) api->CommDestroy(static_cast<ncclComm_t>(g->nccl_comm));
     g->nccl_comm = comm;
     g->rank = rank;
     g->world = world;

@@ -160,10 +160,18 @@ struct pdg_graph {
     std::vector<M3Group> m3_groups;      // groups staged since msd3_reserve
     uint32_t m3_max_groups = 0;
     bool m3_timed = false;
+    // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per DEVICE: remembered per graph (a graph lives on one
+    // device), never in a process-wide static -- a second Engine on another GPU has to set it again
+    uint32_t attr_mask = 0;
+    enum { ATTR_MSD3 = 1, ATTR_MSDLONG = 2, ATTR_RADIX8 = 4, ATTR_RADIX16 = 8, ATTR_KSORT = 16 /* + 4 template bits */ };
     uint64_t m3_pos_lo = 0;
     pdg::DevBuf recA, recB, scratch0, scratch1, scratch2, status, hist;
     pdg::DevBuf q_a, q_b, q_cnt, q_cnt_g, q_off, q_hits, small;
     uint64_t q_n = 0, q_total = 0;
+    bool q_connected = false;            // the last query call was pdg_query_connected
+    pdg::DevBuf qs_len, qs_off, qs_bytes;   // strings of the last query's hits (query.cu)
+    uint64_t qs_total = 0;
+    bool qs_ready = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::vector<cudaEvent_t> k_events;   // per-kernel timing of msd3.cu / ingest_batch.cu
     bool collect_sort_stats = false;   // radix.cu times its pass kernels into stats
@@ -233,6 +241,8 @@ uint64_t sort_unique_keys(pdg_graph *g, uint64_t *keys, uint64_t *tmp, uint64_t 
 int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q, int64_t max_len,
               bool connected_only, uint64_t *total);
 int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_codes, int32_t *status);
+int query_strings_size(pdg_graph *g, uint64_t *total_bytes);
+int query_strings_fetch(pdg_graph *g, uint64_t *h_offsets, uint8_t *h_bytes);
 
 // ---- comm.cu ----
 // in: sorted unique codes of this rank (d_local, n_local); out: g->u_codes_buf holds the global
@@ -240,5 +250,6 @@ int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_
 int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_local, int key_bits, uint64_t *n_global);
 // collective: gathers the global sorted node table into g->u_codes_buf if it is still distributed
 int comm_materialize_nodes(pdg_graph *g);
+void comm_destroy(pdg_graph *g);
 
 }  // namespace pdg

@@ -270,12 +270,12 @@ template <bool IN_GENOME, bool OUT_FINAL>
 static void launch_pass(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, const uint64_t *in, uint64_t n,
                         int shift, uint32_t mask, const uint64_t *base, uint64_t n_tiles, unsigned int *ticket,
                         uint64_t *out_rec, uint32_t *out_pos, uint32_t *row_start) {
-    static bool attr_set = false;
     const size_t smem = sizeof(uint64_t) * KS_TILE + sizeof(uint32_t) * KS_WARPS * 256;
-    if (!attr_set) {
+    const uint32_t which = (uint32_t)pdg_graph::ATTR_KSORT << ((IN_GENOME ? 1 : 0) + (OUT_FINAL ? 2 : 0));   // one bit per instantiation
+    if (!(g->attr_mask & which)) {
         PDG_CUDA(cudaFuncSetAttribute(ksort_pass_kernel<IN_GENOME, OUT_FINAL>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
+        g->attr_mask |= which;
     }
     ksort_pass_kernel<IN_GENOME, OUT_FINAL><<<(unsigned)n_tiles, KS_THREADS, smem, g->stream>>>(
         g->packed.as<unsigned long long>(), g->packed.cap / 8, hc.pos0, hc.pos1, g->k, ct, in, n, shift, mask, base,

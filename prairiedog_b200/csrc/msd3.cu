@@ -413,13 +413,12 @@ void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_g
     g->m3_launched = false;
     g->m3_max_groups = max_groups;
     g->m3_pos_lo = pos_lo;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!(g->attr_mask & pdg_graph::ATTR_MSD3)) {
         PDG_CUDA(cudaFuncSetAttribute(m3_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 1 << 16));
         PDG_CUDA(cudaFuncSetAttribute(m3_pass1_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
         PDG_CUDA(cudaFuncSetAttribute(m3_pass2_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
         PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
-        attr_set = true;
+        g->attr_mask |= pdg_graph::ATTR_MSD3;
     }
 }
 

@@ -263,10 +263,9 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
         PDG_CUDA(cudaEventCreate(&ev));
         g->k_events.push_back(ev);
     }
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!(g->attr_mask & pdg_graph::ATTR_MSDLONG)) {
         PDG_CUDA(cudaFuncSetAttribute(ml_big_bucket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ML_BIG * 12));
-        attr_set = true;
+        g->attr_mask |= pdg_graph::ATTR_MSDLONG;
     }
     const unsigned grid = 148 * 16;                            // warps stride over the buckets
     const unsigned long long *packed = g->packed.as<unsigned long long>();

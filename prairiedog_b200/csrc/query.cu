@@ -204,6 +204,11 @@ __global__ void __launch_bounds__(256) xquery_kernel(XView G, const uint64_t *__
     if (!FILL && lane == 0) counts[q] = (uint32_t)min((uint64_t)counts[q] + total, (uint64_t)0xFFFFFFFFu);
 }
 
+__global__ void q_saturated_kernel(const uint32_t *__restrict__ counts, uint64_t n_q, uint32_t *__restrict__ n_sat) {
+    const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < n_q && counts[q] == 0xFFFFFFFFu) atomicAdd(n_sat, 1u);
+}
+
 int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q, int64_t max_len,
               bool connected_only, uint64_t *total) {
     cudaStream_t s = g->stream;
@@ -213,6 +218,9 @@ int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n
     }
     g->q_n = n_q;
     g->q_total = 0;
+    g->qs_total = 0;
+    g->qs_ready = false;
+    g->q_connected = connected_only;
     *total = 0;
     g->q_off.reserve((n_q + 1) * 8, s);
     if (n_q == 0) {
@@ -242,10 +250,24 @@ int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n
         xquery_kernel<false><<<grid, 256, 0, s>>>(X, qa, qb, n_q, max_len, conn, cnt, cnt_g, nullptr, nullptr);
         PDG_LAUNCHED(g);
     }
+    // the count kernels saturate counts[q] at 2^32 - 1 while the fill kernels write the TRUE number of hits:
+    // a saturated count would let one query run into the next one's slots, so it is an error here
+    g->small.reserve(16, s);
+    PDG_CUDA(cudaMemsetAsync(g->small.p, 0, 4, s));
+    q_saturated_kernel<<<(unsigned)((n_q + 255) / 256), 256, 0, s>>>(cnt, n_q, g->small.as<uint32_t>());
+    PDG_LAUNCHED(g);
     exclusive_scan_u32_u64(cnt, g->q_off.as<uint64_t>(), n_q, g);
     uint64_t tot = 0;
+    uint32_t saturated = 0;
     PDG_CUDA(cudaMemcpyAsync(&tot, g->q_off.as<uint64_t>() + n_q, 8, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaMemcpyAsync(&saturated, g->small.p, 4, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
+    if (saturated) {
+        g->q_n = 0;
+        set_error("query: %u quer%s more than 4294967294 hits each (32-bit hit counts); lower max_len or split the batch",
+                  saturated, saturated == 1 ? "y has" : "ies have");
+        return PDG_E_CAPACITY;
+    }
     g->q_total = tot;
     *total = tot;
     if (tot) {
@@ -322,6 +344,107 @@ int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_
     }
     PDG_CUDA(cudaMemcpyAsync(h_codes, d_codes, n * 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaMemcpyAsync(status, d_st, 4, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    return PDG_OK;
+}
+
+// ---- strings of a batch's hits ---------------------------------------------------------------------------
+// Prairiedog.query (prairiedog/prairiedog.py:22-31) spells every hit with concat_values (prairiedog/node.py:22-37):
+// first node value + last character of every later one = residues [begin + i, begin + j + 1 + k) of the hit's
+// contig.  One pass sizes the strings (16-byte aligned starts so that a warp stores whole uint4), one pass decodes
+// them straight off the 2-bit store: a warp per hit, a lane per 16 characters, 512 contiguous bytes per warp store.
+// Hits of the explicit part need the chain walk of lemon_graph.py:244-264 (node values can be opaque there): they
+// get length 0 here and the host spells them with pdg_query_walk.
+__global__ void qs_len_kernel(const pdg_hit *__restrict__ hits, uint64_t n, int k, uint32_t *__restrict__ len16) {
+    const uint64_t h = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= n) return;
+    const pdg_hit x = hits[h];
+    const uint32_t len = (x.aux & PDG_HIT_EXPLICIT) ? 0u : (uint32_t)(x.j - x.i + 1 + k);
+    len16[h] = (len + 15u) >> 4;
+}
+
+__global__ void __launch_bounds__(256) qs_fill_kernel(const pdg_hit *__restrict__ hits, const uint64_t *__restrict__ off16,
+                                                      uint64_t n, const uint64_t *__restrict__ cbegin,
+                                                      const unsigned long long *__restrict__ packed, int k,
+                                                      uint4 *__restrict__ out) {
+    const uint64_t h = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (h >= n) return;
+    const pdg_hit x = hits[h];
+    if (x.aux & PDG_HIT_EXPLICIT) return;
+    const uint64_t p0 = cbegin[x.aux] + (uint64_t)x.i;
+    const uint32_t len = (uint32_t)(x.j - x.i + 1 + k);
+    uint4 *dst = out + off16[h];
+    for (uint32_t c = 16u * lane; c < len; c += 512u) {
+        // 16 residues from c on as one 32-bit code (reads past the string stay inside the zero-padded store)
+        const uint32_t code = (uint32_t)kmer_at(packed, p0 + c, 16);
+        uint32_t w[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            const uint32_t b = (code >> (24 - 8 * m)) & 0xffu;    // residues 4m .. 4m+3, first one on top
+            const uint32_t sel = (b >> 6) | (((b >> 4) & 3u) << 4) | (((b >> 2) & 3u) << 8) | ((b & 3u) << 12);
+            w[m] = __byte_perm(0x47435441u, 0u, sel);             // "ATCG"[digit], one byte per residue
+            const uint32_t left = len - c > 4u * m ? len - c - 4u * m : 0u;   // characters of the string in this word
+            if (left < 4u) w[m] &= left ? (0xffffffffu >> (32u - 8u * left)) : 0u;
+        }
+        dst[c >> 4] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+// sizes the strings of the hits of the last pdg_query_paths call; *total_bytes = size of the byte buffer
+int query_strings_size(pdg_graph *g, uint64_t *total_bytes) {
+    cudaStream_t s = g->stream;
+    if (!g->finalized) {
+        set_error("pdg_query_strings_size before pdg_finalize");
+        return PDG_E_INVALID;
+    }
+    if (g->q_connected) {
+        set_error("pdg_query_strings_size: the last query was pdg_query_connected (start edges, not paths)");
+        return PDG_E_INVALID;
+    }
+    const uint64_t n = g->q_total;
+    g->qs_off.reserve((n + 1) * 8, s);
+    g->qs_total = 0;
+    if (n == 0) {
+        PDG_CUDA(cudaMemsetAsync(g->qs_off.p, 0, 8, s));
+    } else {
+        g->qs_len.reserve(n * 4, s);
+        qs_len_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(g->q_hits.as<pdg_hit>(), n, g->k, g->qs_len.as<uint32_t>());
+        PDG_LAUNCHED(g);
+        exclusive_scan_u32_u64(g->qs_len.as<uint32_t>(), g->qs_off.as<uint64_t>(), n, g);
+        uint64_t tot16 = 0;
+        PDG_CUDA(cudaMemcpyAsync(&tot16, g->qs_off.as<uint64_t>() + n, 8, cudaMemcpyDeviceToHost, s));
+        PDG_CUDA(cudaStreamSynchronize(s));
+        g->qs_total = tot16 * 16;
+    }
+    g->qs_ready = true;
+    *total_bytes = g->qs_total;
+    return PDG_OK;
+}
+
+// h_offsets[n_hits + 1]: byte offset of every hit's string (its length is j - i + 1 + k; 0 for explicit hits);
+// h_bytes: qs_total bytes.  h_bytes may be pinned memory (one cudaMemcpyAsync straight into it).
+int query_strings_fetch(pdg_graph *g, uint64_t *h_offsets, uint8_t *h_bytes) {
+    cudaStream_t s = g->stream;
+    if (!g->qs_ready) {
+        set_error("pdg_query_strings_fetch before pdg_query_strings_size");
+        return PDG_E_INVALID;
+    }
+    const uint64_t n = g->q_total;
+    if (g->qs_total) {
+        g->qs_bytes.reserve(g->qs_total, s);
+        const ContigTable ct = g_table(g);
+        qs_fill_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, s>>>(g->q_hits.as<pdg_hit>(), g->qs_off.as<uint64_t>(), n,
+                                                                       ct.begin, g->packed.as<unsigned long long>(), g->k,
+                                                                       g->qs_bytes.as<uint4>());
+        PDG_LAUNCHED(g);
+        if (h_bytes) PDG_CUDA(cudaMemcpyAsync(h_bytes, g->qs_bytes.p, g->qs_total, cudaMemcpyDeviceToHost, s));
+    }
+    if (h_offsets) {
+        PDG_CUDA(cudaMemcpyAsync(h_offsets, g->qs_off.p, (n + 1) * 8, cudaMemcpyDeviceToHost, s));
+        PDG_CUDA(cudaStreamSynchronize(s));
+        for (uint64_t i = 0; i <= n; ++i) h_offsets[i] *= 16;   // the device keeps them in 16-byte units
+    }
     PDG_CUDA(cudaStreamSynchronize(s));
     return PDG_OK;
 }

@@ -209,11 +209,10 @@ static Rec *radix_sort_impl(pdg_graph *g, Rec *a, Rec *b, uint64_t n, const std:
     PDG_CUDA(cudaMemcpyAsync(d_base, h_base.data(), hist_bytes, cudaMemcpyHostToDevice, s));
 
     const size_t smem = sizeof(Rec) * RS_TILE + sizeof(uint32_t) * RS_WARPS * 256;
-    static bool attr_set[2] = {false, false};
-    const int which = sizeof(Rec) == 16 ? 1 : 0;
-    if (!attr_set[which]) {
+    const uint32_t which = sizeof(Rec) == 16 ? pdg_graph::ATTR_RADIX16 : pdg_graph::ATTR_RADIX8;
+    if (!(g->attr_mask & which)) {
         PDG_CUDA(cudaFuncSetAttribute(onesweep_kernel<Rec>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set[which] = true;
+        g->attr_mask |= which;
     }
     const size_t status_bytes = n_tiles * 256 * sizeof(unsigned long long);
     g->status.reserve(status_bytes, s);

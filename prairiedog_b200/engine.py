@@ -204,6 +204,7 @@ class Engine(object):
         a, b = _u64(a), _u64(b)
         tot = ctypes.c_uint64()
         check(fn(self.h, a.ctypes.data, b.ctypes.data, a.size, *extra, ctypes.byref(tot)))
+        self._last_hits = tot.value
         off = np.zeros(a.size + 1, dtype=np.uint64)
         hits = np.zeros(tot.value, dtype=HIT_DTYPE)
         check(self.lib.pdg_query_fetch(self.h, off.ctypes.data, hits.ctypes.data if tot.value else None))
@@ -225,6 +226,19 @@ class Engine(object):
         st = ctypes.c_int32()
         check(self.lib.pdg_query_walk(self.h, int(src_code), ctypes.byref(h), out.ctypes.data, ctypes.byref(st)))
         return out, st.value
+
+    def query_strings(self):
+        """Strings of every hit of the last query_paths call (pdg_query_strings_*): (offsets[n_hits+1] in bytes,
+        uint8 array).  Hit h's string is bytes[off[h] : off[h] + (j - i + 1 + k)]; explicit-part hits have none."""
+        import torch
+        tot = ctypes.c_uint64()
+        check(self.lib.pdg_query_strings_size(self.h, ctypes.byref(tot)))
+        n = int(self._last_hits)
+        off = np.zeros(n + 1, dtype=np.uint64)
+        # pinned: one cudaMemcpyAsync straight into it (a pageable numpy array halves the copy rate)
+        buf = torch.empty(max(tot.value, 1), dtype=torch.uint8, pin_memory=True)
+        check(self.lib.pdg_query_strings_fetch(self.h, off.ctypes.data, buf.data_ptr() if tot.value else None))
+        return off, buf.numpy()[:tot.value]
 
     # ---- multi GPU ----
     def comm_unique_id(self):

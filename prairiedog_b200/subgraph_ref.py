@@ -36,8 +36,10 @@ class SubgraphRef:
         from .b200_graph import B200Graph
         if isinstance(self.graph, B200Graph) and not encode and getattr(km, "well_formed", False):
             c = self.graph.add_genome(km)
-            # the reference leaves the iterator exhausted (subgraph_ref.py:51)
-            km.li, km.pi = len(km.sequences) - 1, len(km.sequences[-1]) - km.k + 1
+            # the reference leaves the iterator exhausted (subgraph_ref.py:51); the contig lengths are in the
+            # layout already -- km.sequences would read the whole genome back from the device and decode it
+            lens = km.layout.seq_len
+            km.li, km.pi = int(lens.size) - 1, int(lens[-1]) - km.k + 1
             return c
         implicit_nodes = isinstance(self.graph, B200Graph)   # like LGGraph: add_edge upserts endpoints
         c = 0

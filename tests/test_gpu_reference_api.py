@@ -97,6 +97,51 @@ def test_unsaved_data_is_invisible(env):
     assert g.connected(nm["ABC"], nm["BCD"])[0]
 
 
+@pytest.mark.parametrize("n_more", [3, 70000], ids=["few-staged-edges", "more-than-one-flush"])
+def test_queries_after_save_then_add_see_the_committed_state(env, n_more):
+    """save -> add -> query: LemonGraph answers from the last COMMITTED state while the write transaction is open
+    (lemon_graph.py:178-180 vs :54-64), whatever the amount of uncommitted data.  (70000 staged edges cross the
+    65536-edge flush into libpdgpu, which used to turn the query into 'query before pdg_finalize'.)"""
+    from prairiedog_b200 import Edge
+    g, nm = env
+    g.add_edge(Edge(nm["ABC"], nm["BCD"], edge_value=0))
+    g.save()
+    assert g.connected(nm["ABC"], nm["BCD"])[0]
+    g.add_edge(Edge(nm["BCD"], nm["CDE"], edge_value=1))
+    for i in range(n_more):
+        g.add_edge(Edge(nm["CDE"], nm["DEF"], edge_value=2 + i), echo=False)
+    # uncommitted: invisible; committed: still there
+    assert g.connected(nm["BCD"], nm["CDE"]) == (False, ())
+    assert g.path(nm["ABC"], nm["CDE"]) == ((), ())
+    ok, starts = g.connected(nm["ABC"], nm["BCD"])
+    assert ok and len(starts) == 1
+    assert len(g.path(nm["ABC"], nm["BCD"])[0]) == 1
+    g.save()
+    assert g.connected(nm["BCD"], nm["CDE"])[0]
+    assert len(g.path(nm["ABC"], nm["CDE"])[0]) == 1
+    assert g.engine.counts()[1] == 2 + n_more
+
+
+def test_bulk_add_after_save_keeps_the_committed_index(lib_built):
+    """the same for the bulk path: a genome added after save() is invisible until the next save()"""
+    import numpy as np
+    from conftest import data_path
+    from prairiedog_b200 import B200Graph, codec
+    g = B200Graph(k=11)
+    g.add_fasta(data_path("syn101.fasta"))
+    g.save()
+    before = g.engine.counts()
+    seq = g.engine.fetch_residues(0, 80)
+    a, b = seq[3:14], seq[20:31]
+    hits_before = g.path_many([(a, b)])[2]
+    assert len(hits_before) >= 1
+    g.add_fasta(data_path("syn102.fasta"))
+    assert g.engine.counts() == before                       # counts of the committed graph
+    assert np.array_equal(g.path_many([(a, b)])[2], hits_before)
+    g.save()
+    assert g.engine.counts()[2] > before[2]
+
+
 def test_graph_basics_nodes(env):
     """tests/test_graph.py:16-23."""
     from prairiedog_b200 import Node
