@@ -49,6 +49,7 @@ class B200Graph(Graph):
         self.engine = Engine(k, device)
         # lemon_graph.py:229-236 skips a pair when its length exceeds sys.getrecursionlimit()
         self.path_limit = sys.getrecursionlimit() if path_limit is None else path_limit
+        self._dist = None           # (rank, world, device) once distributed.attach() opened the communicator
         self._reset_host()
 
     def _reset_host(self):
@@ -67,6 +68,7 @@ class B200Graph(Graph):
         self._st_src, self._st_tgt, self._st_type, self._st_val, self._st_nodes = [], [], [], [], []
         self._unsaved = False
         self._published = False     # nothing saved yet: queries see an empty graph
+        self._type_bases = None     # multi-rank: global type numbering, agreed at the first query after a save()
 
     # ------------------------------------------------------------------ interning
     def _key(self, value, create=True):
@@ -183,6 +185,7 @@ class B200Graph(Graph):
         self.engine.finalize()
         self._unsaved = False
         self._published = True
+        self._type_bases = None
 
     def snapshot(self, f: str) -> str:
         """Publishes and writes the graph to ``f`` (the role of the LMDB file the Snakefile copies to
@@ -424,7 +427,19 @@ class B200Graph(Graph):
                         dtype=np.uint64)
 
     def connected_many(self, pairs):
-        """Batched connected(): list of (bool, tuple[Edge]) in the order of ``pairs``."""
+        """Batched connected(): list of (bool, tuple[Edge]) in the order of ``pairs``.  Multi-rank: collective, the
+        start edges of every rank's shard in rank order."""
+        out = self._connected_many_local(pairs)
+        if self._dist is not None:
+            from . import distributed
+            parts = distributed.gather_objects(out)
+            out = []
+            for q in range(len(pairs)):
+                edges = sum((tuple(p[q][1]) for p in parts), ())
+                out.append((len(edges) > 0, edges))
+        return out
+
+    def _connected_many_local(self, pairs):
         a = self._codes([p[0] for p in pairs])
         b = self._codes([p[1] for p in pairs])
         if not self._published:
@@ -447,20 +462,34 @@ class B200Graph(Graph):
         """lemon_graph.py:178-219."""
         return self.connected_many([(node_a, node_b)])[0]
 
-    def path_many(self, pairs, limit=None):
-        """Batched path(): list of hit lists [(edge_type, i, j)] -- no Node objects are built."""
+    def path_many(self, pairs, limit=None, local=False):
+        """Batched path(): (codes of the a's, offsets[n_pairs + 1], hit records {type_id, i, j, aux}) -- no Node
+        objects are built.  In a multi-rank job (distributed.attach) the call is COLLECTIVE: every rank passes the
+        same pairs, runs them against its own shard and receives the hits of the whole pangenome, type ids in the
+        global numbering (``self.hit_owner`` then names the rank that holds each hit's contig); ``local=True``
+        keeps the answer of this rank's shard."""
         a = self._codes([p[0] for p in pairs])
         b = self._codes([p[1] for p in pairs])
         if not self._published:
             from .engine import HIT_DTYPE
-            return a, np.zeros(len(pairs) + 1, dtype=np.uint64), np.zeros(0, dtype=HIT_DTYPE)
-        off, hits = self.engine.query_paths(a, b, self.path_limit if limit is None else limit)
+            off, hits = np.zeros(len(pairs) + 1, dtype=np.uint64), np.zeros(0, dtype=HIT_DTYPE)
+        else:
+            off, hits = self.engine.query_paths(a, b, self.path_limit if limit is None else limit)
+        self.hit_owner = None
+        if self._dist is not None and not local:
+            from . import distributed
+            rank, world, dev = self._dist
+            if self._type_bases is None:
+                self._type_bases = distributed.type_bases(self._next_type, dev)
+            off, hits, self.hit_owner = distributed.exchange_hits(off, hits, int(self._type_bases[rank]), dev)
         return a, off, hits
 
     def query_many(self, pairs, limit=None, strings=True):
         """Prairiedog.query (prairiedog.py:17-33) for a batch of (src, dst) pairs: per pair the list of
         hit dicts {'string', 'edge_type', 'i', 'j'}; 'string' is concat_values (node.py:22-37) of the
         hit's node chain, spelled from the codes without building Node objects."""
+        if self._dist is not None:
+            return self._query_many_distributed(pairs, limit, strings)
         a, off, hits = self.path_many(pairs, limit)
         spell = self._hit_strings(a, off, hits) if strings else None
         out = []
@@ -474,6 +503,29 @@ class B200Graph(Graph):
                 row.append(d)
             out.append(row)
         return out
+
+    def _query_many_distributed(self, pairs, limit, strings):
+        """query_many over an N-rank graph (collective): every rank spells the hits of ITS shard -- the labels and
+        the residues live there -- and the rows are concatenated in rank order, which is the order a single-process
+        graph returns them in."""
+        from . import distributed
+        a, off, hits = self.path_many(pairs, limit, local=True)
+        spell = self._hit_strings(a, off, hits) if strings else None
+        rank, world, dev = self._dist
+        if self._type_bases is None:
+            self._type_bases = distributed.type_bases(self._next_type, dev)
+        tid, hi, hj = hits["type_id"].tolist(), hits["i"].tolist(), hits["j"].tolist()
+        mine = []
+        for q in range(len(pairs)):
+            row = []
+            for x in range(int(off[q]), int(off[q + 1])):
+                d = {'edge_type': self._type_string(tid[x]), 'i': hi[x], 'j': hj[x]}
+                if strings:
+                    d['string'] = spell[x]
+                row.append(d)
+            mine.append(row)
+        parts = distributed.gather_objects(mine)
+        return [sum((parts[r][q] for r in range(world)), []) for q in range(len(pairs))]
 
     def _hit_strings(self, a, off, hits):
         """concat_values (node.py:22-37) of every hit of the LAST path_many call: genome-part hits are decoded on
@@ -501,8 +553,17 @@ class B200Graph(Graph):
         return out
 
     def path(self, node_a: str, node_b: str) -> typing.Tuple[tuple, tuple]:
-        """lemon_graph.py:275-334."""
-        a, off, hits = self.path_many([(node_a, node_b)])
+        """lemon_graph.py:275-334.  Multi-rank: collective, the paths of every rank's shard in rank order."""
+        paths, metas = self._path_local(node_a, node_b)
+        if self._dist is not None:
+            from . import distributed
+            parts = distributed.gather_objects((paths, metas))
+            paths = sum((tuple(p[0]) for p in parts), ())
+            metas = sum((tuple(p[1]) for p in parts), ())
+        return paths, metas
+
+    def _path_local(self, node_a, node_b):
+        a, off, hits = self.path_many([(node_a, node_b)], local=True)
         paths, metas = [], []
         spell = self._hit_strings(a, off, hits)
         k = self.k

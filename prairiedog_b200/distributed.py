@@ -11,7 +11,11 @@ conventions the CUDA side (csrc/comm.cu) relies on:
 * ``bind_host_to_device``  pins the process to the CPUs local to its GPU before pinned buffers are allocated;
 * ``attach``     hands every rank the same 128-byte NCCL id through ``torch.distributed`` (NCCL on
                  the GPU box, gloo in the CPU tests) and opens the library's communicator;
-* ``reduce_counts``  whole-job edge / k-mer counts (nodes are already global after ``save()``).
+* ``reduce_counts``  whole-job edge / k-mer counts (nodes are already global after ``save()``);
+* ``type_bases`` / ``exchange_hits`` / ``type_strings``  the path query over an N-rank graph: every rank holds the
+                 occurrence index of ITS genomes only, and a hit (edge_type, i, j) lives entirely inside one contig,
+                 so the hits of a pair are the concatenation over the ranks of what each rank finds in its shard
+                 (prairiedog/lemon_graph.py:275-334 answers over the whole pangenome; SURVEY.md 8(e) "Queries").
 
 torch.distributed is plumbing only; the data path collective is the grouped ncclSend/ncclRecv inside
 ``pdg_finalize``.
@@ -95,7 +99,8 @@ def bind_host_to_device(index):
 
 
 def attach(graph, device=None):
-    """Opens the NCCL communicator of ``graph`` (a B200Graph) for the current process group.
+    """Opens the NCCL communicator of ``graph`` (a B200Graph) for the current process group and makes its
+    queries collective (B200Graph.path_many / query_many then answer over all ranks' shards).
     No-op for a single rank."""
     import torch.distributed as dist
     if not dist.is_available() or not dist.is_initialized() or dist.get_world_size() == 1:
@@ -104,7 +109,104 @@ def attach(graph, device=None):
     uid = graph.engine.comm_unique_id() if rank == 0 else np.zeros(128, dtype=np.uint8)
     uid = broadcast_bytes(uid, 0, device)
     graph.engine.comm_init(uid, rank, world)
+    graph._dist = (rank, world, device)
     return rank, world
+
+
+# ------------------------------------------------------------------ queries over an N-rank graph
+def _world():
+    import torch.distributed as dist
+    if not dist.is_available() or not dist.is_initialized():
+        return 0, 1
+    return dist.get_rank(), dist.get_world_size()
+
+
+def _all_gather_i64(vec, device=None):
+    """every rank's int64 vector (equal lengths) -> array [world, n]"""
+    import torch
+    import torch.distributed as dist
+    rank, world = _world()
+    t = torch.from_numpy(np.ascontiguousarray(vec, dtype=np.int64))
+    if world == 1:
+        return t.numpy()[None, :]
+    if device is not None:
+        t = t.to(device)
+    out = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(out, t)
+    return np.stack([o.cpu().numpy() for o in out])
+
+
+def type_bases(n_types, device=None):
+    """Global edge-type numbering: rank r's local type id t is the global id bases[r] + t, bases = exclusive prefix of
+    every rank's type count (ranks hold contiguous blocks of the genome list, so global ids ascend with the genome
+    order like the ids of a single-process graph that loaded the same files in order).  Collective.
+    Returns bases[world + 1]."""
+    counts = _all_gather_i64([int(n_types)], device)[:, 0]
+    return np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+
+
+def merge_hits(counts, hits_per_rank):
+    """Pure host step of exchange_hits.  counts[r][q]: hits rank r found for pair q; hits_per_rank[r]: its hit
+    records, grouped by pair, already carrying GLOBAL type ids.  Returns (offsets[n_q + 1], hits, owner) with the
+    hits of a pair in rank order -- the order a single-process graph returns them in (ascending genome)."""
+    counts = np.asarray(counts, dtype=np.int64)
+    world, n_q = counts.shape
+    off = np.zeros(n_q + 1, dtype=np.int64)
+    np.cumsum(counts.sum(axis=0), out=off[1:])
+    total = int(off[-1])
+    dtype = hits_per_rank[0].dtype
+    hits = np.zeros(total, dtype=dtype)
+    owner = np.zeros(total, dtype=np.int32)
+    before = np.zeros(n_q, dtype=np.int64)          # hits of the same pair on lower ranks
+    for r in range(world):
+        c = counts[r]
+        n_r = int(c.sum())
+        if n_r:
+            loc_off = np.concatenate([[0], np.cumsum(c)])[:-1]
+            qof = np.repeat(np.arange(n_q), c)
+            dest = off[qof] + before[qof] + (np.arange(n_r) - loc_off[qof])
+            hits[dest] = hits_per_rank[r][:n_r]
+            owner[dest] = r
+        before += c
+    return off.astype(np.uint64), hits, owner
+
+
+def exchange_hits(off, hits, type_base, device=None):
+    """Collective.  Every rank ran the SAME pair batch against its own shard: off[n_q + 1] / hits are its local
+    result (local type ids).  Returns (offsets, hits, owner) of the whole graph on every rank: global type ids
+    (+ type_base), `aux` stays local to the owner rank (owner[h] says which).  Two all-gathers: the per-pair counts,
+    then the hit records padded to the largest rank."""
+    import torch
+    import torch.distributed as dist
+    rank, world = _world()
+    off = np.asarray(off).astype(np.int64)
+    mine = hits.copy()
+    mine["type_id"] += np.uint32(type_base)
+    counts = _all_gather_i64(np.diff(off), device)
+    if world == 1:
+        return merge_hits(counts, [mine])
+    totals = counts.sum(axis=1)
+    cap = max(int(totals.max()), 1)
+    send = np.zeros((cap, 4), dtype=np.int32)
+    send[:mine.size] = mine.view(np.int32).reshape(-1, 4)
+    t = torch.from_numpy(send)
+    if device is not None:
+        t = t.to(device)
+    recv = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(recv, t)
+    parts = [recv[r].cpu().numpy().reshape(-1).view(mine.dtype)[:int(totals[r])] for r in range(world)]
+    return merge_hits(counts, parts)
+
+
+def gather_objects(obj):
+    """all_gather_object (strings of the hits a rank owns, type labels): list indexed by rank"""
+    import torch.distributed as dist
+    rank, world = _world()
+    if world == 1:
+        return [obj]
+    out = [None] * world
+    dist.all_gather_object(out, obj)
+    return out
 
 
 def reduce_counts(values, device=None, op="sum"):

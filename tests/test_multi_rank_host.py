@@ -78,6 +78,94 @@ def _worker(rank, world, port, k, out_dir):
         dist.destroy_process_group()
 
 
+def _query_worker(rank, world, port, k, out_dir):
+    """The path query over an N-rank graph, host side: every rank answers the same pair batch from the C oracle of
+    ITS shard (standing in for its GPU), distributed.exchange_hits merges over gloo; rank 0 compares with the oracle
+    of all files in one graph."""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    from oracle.c_oracle import COracle
+    from prairiedog_b200 import distributed as D
+    from prairiedog_b200.engine import HIT_DTYPE
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        paths = [data_path(f) for f in FILES]
+        whole = COracle(k)
+        for p in paths:
+            whole.add_fasta(p)
+        whole.build()
+        codes, rowptr, pos = whole.index()
+        rng = np.random.default_rng(5)                      # same pairs on every rank
+        # code of the k-mer starting at every residue position (-1: no k-mer starts there, i.e. a contig tail)
+        code_at = np.full(int(pos.max()) + 2, -1, dtype=np.int64)
+        code_at[pos] = np.repeat(codes, np.diff(rowptr.astype(np.int64))).astype(np.int64)
+        qa, qb = [], []
+        while len(qa) < 30:                                 # positives: b starts d residues after a, same contig
+            p0, d = int(rng.integers(0, code_at.size - 60)), int(rng.integers(1, 50))
+            if (code_at[p0:p0 + d + 1] >= 0).all():
+                qa.append(code_at[p0])
+                qb.append(code_at[p0 + d])
+        for _ in range(10):                                 # and unrelated pairs
+            qa.append(code_at[pos[int(rng.integers(0, pos.size))]])
+            qb.append(code_at[pos[int(rng.integers(0, pos.size))]])
+        qa, qb = np.array(qa, dtype=np.uint64), np.array(qb, dtype=np.uint64)
+        mine = COracle(k)
+        for p in D.shard(paths, rank, world):
+            mine.add_fasta(p)
+        mine.build()
+        bases = D.type_bases(mine.n_types)
+        assert bases[-1] == whole.n_types and bases[0] == 0
+        off, rows = [0], []
+        for a, b in zip(qa.tolist(), qb.tolist()):
+            h = mine.query(a, b, 200)
+            rows += [(t, i, j, 0) for t, i, j in h.tolist()]
+            off.append(len(rows))
+        local = np.array(rows, dtype=HIT_DTYPE) if rows else np.zeros(0, dtype=HIT_DTYPE)
+        goff, ghits, owner = D.exchange_hits(np.array(off, dtype=np.uint64), local, int(bases[rank]))
+        # every rank receives the same global answer
+        want_off, want = [0], []
+        for a, b in zip(qa.tolist(), qb.tolist()):
+            want += [tuple(x) for x in whole.query(a, b, 200).tolist()]
+            want_off.append(len(want))
+        assert goff.tolist() == want_off
+        got = [(int(h["type_id"]), int(h["i"]), int(h["j"])) for h in ghits]
+        for q in range(40):                                 # per pair: the same hits in the same order
+            assert got[want_off[q]:want_off[q + 1]] == want[want_off[q]:want_off[q + 1]], q
+        assert len(want) > 0 and set(owner.tolist()) == set(range(world))
+        # the owner is the rank whose type range holds the hit
+        assert (np.searchsorted(bases, ghits["type_id"].astype(np.int64), side="right") - 1 == owner).all()
+        assert D.gather_objects(rank) == list(range(world))
+        open(os.path.join(out_dir, "ok%d" % rank), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_world_size_2_query_exchange_gloo(tmp_path):
+    import torch.multiprocessing as mp
+    mp.spawn(_query_worker, args=(2, _free_port(), 11, str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
+def test_merge_hits_orders_by_pair_then_rank():
+    from prairiedog_b200 import distributed as D
+    from prairiedog_b200.engine import HIT_DTYPE
+    r0 = np.array([(0, 1, 2, 0), (0, 3, 4, 0), (1, 5, 6, 0)], dtype=HIT_DTYPE)      # pair 0: 2 hits, pair 2: 1 hit
+    r1 = np.array([(7, 0, 0, 0), (8, 1, 1, 0), (9, 2, 2, 0)], dtype=HIT_DTYPE)      # pair 0: 1, pair 1: 2
+    off, hits, owner = D.merge_hits([[2, 0, 1], [1, 2, 0]], [r0, r1])
+    assert off.tolist() == [0, 3, 5, 6]
+    assert hits["type_id"].tolist() == [0, 0, 7, 8, 9, 1]
+    assert owner.tolist() == [0, 0, 1, 1, 1, 0]
+    off, hits, owner = D.merge_hits([[0, 0]], [np.zeros(0, dtype=HIT_DTYPE)])
+    assert off.tolist() == [0, 0, 0] and hits.size == 0
+    # single process: exchange_hits only applies the type base
+    off, hits, owner = D.exchange_hits(np.array([0, 2, 3], dtype=np.uint64), r0, 10)
+    assert hits["type_id"].tolist() == [10, 10, 11] and off.tolist() == [0, 2, 3] and r0["type_id"].tolist() == [0, 0, 1]
+
+
 def test_shard_covers_every_genome_once():
     from prairiedog_b200 import distributed as D
     for n in (0, 1, 5, 8, 100):
