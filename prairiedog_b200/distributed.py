@@ -171,31 +171,63 @@ def merge_hits(counts, hits_per_rank):
     return off.astype(np.uint64), hits, owner
 
 
+def merge_hits_torch(counts, recv, totals):
+    """merge_hits with torch ops on whatever device the tensors live on (the GPU under NCCL): counts [world, n_q]
+    int64, recv[r] [cap, 4] int32 hit records of rank r, totals[r] how many of them are real.  Returns tensors
+    (offsets [n_q + 1] int64, hits [total, 4] int32, owner [total] int32)."""
+    import torch
+    world, n_q = counts.shape
+    dev = counts.device
+    off = torch.zeros(n_q + 1, dtype=torch.int64, device=dev)
+    torch.cumsum(counts.sum(dim=0), 0, out=off[1:])
+    total = int(off[-1].item())
+    hits = torch.zeros((total, 4), dtype=torch.int32, device=dev)
+    owner = torch.zeros(total, dtype=torch.int32, device=dev)
+    before = torch.cumsum(counts, 0) - counts             # hits of the same pair on lower ranks
+    pairs = torch.arange(n_q, device=dev)
+    for r in range(world):
+        n_r = int(totals[r])
+        if n_r == 0:
+            continue
+        c = counts[r]
+        loc_off = torch.cumsum(c, 0) - c
+        qof = torch.repeat_interleave(pairs, c, output_size=n_r)
+        dest = off[qof] + before[r][qof] + (torch.arange(n_r, device=dev) - loc_off[qof])
+        hits[dest] = recv[r][:n_r]
+        owner[dest] = r
+    return off, hits, owner
+
+
 def exchange_hits(off, hits, type_base, device=None):
     """Collective.  Every rank ran the SAME pair batch against its own shard: off[n_q + 1] / hits are its local
     result (local type ids).  Returns (offsets, hits, owner) of the whole graph on every rank: global type ids
-    (+ type_base), `aux` stays local to the owner rank (owner[h] says which).  Two all-gathers: the per-pair counts,
-    then the hit records padded to the largest rank."""
+    (+ type_base), `aux` stays local to the owner rank (owner[h] says which).  Two all-gathers -- the per-pair counts,
+    then the hit records padded to the largest rank -- and a merge into pair order on ``device`` (merge_hits_torch;
+    the numpy merge_hits states the same step and is what the tests compare it with)."""
     import torch
     import torch.distributed as dist
     rank, world = _world()
     off = np.asarray(off).astype(np.int64)
     mine = hits.copy()
     mine["type_id"] += np.uint32(type_base)
-    counts = _all_gather_i64(np.diff(off), device)
     if world == 1:
-        return merge_hits(counts, [mine])
-    totals = counts.sum(axis=1)
-    cap = max(int(totals.max()), 1)
-    send = np.zeros((cap, 4), dtype=np.int32)
-    send[:mine.size] = mine.view(np.int32).reshape(-1, 4)
-    t = torch.from_numpy(send)
+        return merge_hits(np.diff(off)[None, :], [mine])
+    c = torch.from_numpy(np.diff(off))
     if device is not None:
-        t = t.to(device)
-    recv = [torch.empty_like(t) for _ in range(world)]
-    dist.all_gather(recv, t)
-    parts = [recv[r].cpu().numpy().reshape(-1).view(mine.dtype)[:int(totals[r])] for r in range(world)]
-    return merge_hits(counts, parts)
+        c = c.to(device)
+    cs = [torch.empty_like(c) for _ in range(world)]
+    dist.all_gather(cs, c)
+    counts = torch.stack(cs)
+    totals = counts.sum(dim=1).cpu().tolist()
+    cap = max(int(max(totals)), 1)
+    send = torch.zeros((cap, 4), dtype=torch.int32, device=c.device)
+    if mine.size:
+        send[:mine.size] = torch.from_numpy(mine.view(np.int32).reshape(-1, 4)).to(c.device)
+    recv = [torch.empty_like(send) for _ in range(world)]
+    dist.all_gather(recv, send)
+    goff, ghits, owner = merge_hits_torch(counts, recv, totals)
+    return (goff.cpu().numpy().astype(np.uint64), ghits.cpu().numpy().reshape(-1).view(mine.dtype),
+            owner.cpu().numpy())
 
 
 def gather_objects(obj):

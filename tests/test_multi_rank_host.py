@@ -166,6 +166,32 @@ def test_merge_hits_orders_by_pair_then_rank():
     assert hits["type_id"].tolist() == [10, 10, 11] and off.tolist() == [0, 2, 3] and r0["type_id"].tolist() == [0, 0, 1]
 
 
+def test_merge_hits_torch_equals_numpy_merge():
+    """the device merge of exchange_hits against the plain numpy statement of the same step"""
+    import torch
+    from prairiedog_b200 import distributed as D
+    from prairiedog_b200.engine import HIT_DTYPE
+    rng = np.random.default_rng(11)
+    for world, n_q in ((1, 5), (2, 40), (3, 17), (8, 300)):
+        counts = rng.integers(0, 6, size=(world, n_q))
+        counts[rng.integers(0, world), :] = 0 if world > 1 else counts[0]          # an idle rank
+        parts, recv = [], []
+        cap = max(int(counts.sum(axis=1).max()), 1)
+        for r in range(world):
+            n = int(counts[r].sum())
+            h = np.zeros(n, dtype=HIT_DTYPE)
+            h["type_id"], h["i"], h["j"], h["aux"] = 1000 * r + rng.integers(0, 99, n), rng.integers(0, 9999, n), rng.integers(0, 9999, n), r
+            parts.append(h)
+            pad = np.zeros((cap, 4), dtype=np.int32)
+            pad[:n] = h.view(np.int32).reshape(-1, 4)
+            recv.append(torch.from_numpy(pad))
+        off, hits, owner = D.merge_hits(counts, parts)
+        toff, thits, towner = D.merge_hits_torch(torch.from_numpy(counts.astype(np.int64)), recv, counts.sum(axis=1).tolist())
+        assert toff.tolist() == off.tolist()
+        assert np.array_equal(thits.numpy().reshape(-1).view(HIT_DTYPE), hits)
+        assert towner.tolist() == owner.tolist()
+
+
 def test_shard_covers_every_genome_once():
     from prairiedog_b200 import distributed as D
     for n in (0, 1, 5, 8, 100):
