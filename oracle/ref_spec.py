@@ -145,6 +145,18 @@ class SpecGraph(object):
     def canonical(self):
         return sorted(self.nodes), sorted(self.edges)
 
+    def filter(self, bottom_percentile=0.9):
+        """Graph.filter() as the one backend that implements it defines it (prairiedog/networkx_graph.py:53-75;
+        LGGraph.filter is `pass`, lemon_graph.py:172-173): drop the nodes of low degree, then the isolates.  The
+        labelled multigraph is read as the nx.Graph that backend keeps (networkx_graph.py:11-26: undirected, one
+        edge per node pair whatever the labels), nodes go together with every labelled edge that touches them.
+        Returns the node values that were removed."""
+        keep = filter_keep(self.nodes, ((e[0], e[1]) for e in self.edges), bottom_percentile)
+        gone = self.nodes - keep
+        self.nodes = set(keep)
+        self.edges = set(e for e in self.edges if e[0] in keep and e[1] in keep)
+        return gone
+
     def out_edges(self, a):
         return [e for e in self.edges if e[0] == a]
 
@@ -206,6 +218,31 @@ class SpecGraph(object):
         for edge_type, _, _, nodes in self.path(a, b, limit):
             out.append((concat_values(nodes), edge_type))
         return sorted(out)
+
+
+def filter_keep(nodes, pairs, bottom_percentile=0.9):
+    """Node values that survive prairiedog/networkx_graph.py:53-75 on the undirected simple graph with the given
+    nodes and (a, b) pairs.
+      :53-67  _filter_degree: max_degrees = max degree; bottom_degrees = int(bottom_percentile * max_degrees);
+              remove every node with degree <= bottom_degrees
+      :69-71  _filter_isolates: remove every node left without a neighbour
+    Degree is networkx's: number of distinct neighbours, a self-loop counting twice (nx.Graph.degree)."""
+    nodes = set(nodes)
+    adj = dict((v, set()) for v in nodes)
+    for a, b in pairs:
+        adj.setdefault(a, set()).add(b)
+        adj.setdefault(b, set()).add(a)
+    nodes = set(adj)
+    if not nodes:
+        return set()
+
+    def degree(v, alive):
+        return sum(2 if u == v else 1 for u in adj[v] if u in alive)
+
+    max_degrees = max(degree(v, nodes) for v in nodes)
+    bottom_degrees = int(bottom_percentile * max_degrees)
+    keep = set(v for v in nodes if degree(v, nodes) > bottom_degrees)
+    return set(v for v in keep if degree(v, keep) > 0)
 
 
 def concat_values(values, additional=1):

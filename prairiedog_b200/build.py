@@ -29,8 +29,10 @@ def needs_build():
     return any(os.path.getmtime(p) > t for p in _deps())
 
 
-def build_library(force=False, verbose=True, extra_flags=(), out=None, tag=""):
-    """extra_flags / out / tag: tuning variants (tools/tune_msd3.py) built next to the product library."""
+def build_library(force=False, verbose=True, extra_flags=(), out=None, tag="", csrc=None):
+    """extra_flags / out / tag / csrc: tuning variants (tools/tune_msd3.py) built next to the product library;
+    csrc = another source directory (for example an earlier revision of the kernels, for A/B timing)."""
+    csrc = csrc or CSRC
     if out is None:
         out = LIB
         if not force and not needs_build():
@@ -41,7 +43,7 @@ def build_library(force=False, verbose=True, extra_flags=(), out=None, tag=""):
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     for src in SOURCES:
         obj = os.path.join(HERE, "build", src.replace(".cu", tag + ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + ["-c", os.path.join(csrc, src), "-o", obj]
         if verbose:
             print(" ".join(cmd))
         procs.append((src, subprocess.Popen(cmd)))

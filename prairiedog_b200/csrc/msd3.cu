@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(256) m3_scan_chunks_kernel(uint32_t *__restric
 }
 
 // ---- pass 1: position tile -> records grouped by d3 ---------------------------------------------
+// FULL tile = every window of the tile is a k-mer (tile_info's M3_SIMPLE): no validity words, no guards.
 template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uint2 *__restrict__ packed,
                                                                  uint64_t packed_words, int k, int kv, ContigTable ct, M3Plan pl,
@@ -182,7 +183,7 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uin
                                                                  const uint32_t *__restrict__ O1T,
                                                                  uint64_t *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char m3_raw[];
-    M3Smem &sm = *reinterpret_cast<M3Smem *>(m3_raw);
+    M3Smem2 &sm = *reinterpret_cast<M3Smem2 *>(m3_raw);
     __shared__ uint2 words[M3_TILE_WORDS + 2];
     __shared__ uint32_t vm[M3_TILE_WORDS];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -190,26 +191,30 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uin
     const int sh3 = pl.b1 + pl.b2;
     const uint64_t w0 = (pl.base0 >> 5) + (uint64_t)tile * M3_TILE_WORDS;
     const uint32_t info = tile_info[tile];
+    const bool full = (info & M3_SIMPLE) != 0;          // the same for the whole CTA
     for (int i = tid; i < M3_TILE_WORDS + 2; i += M3_THREADS)
         words[i] = w0 + i < packed_words ? packed[w0 + i] : make_uint2(0u, 0u);
     static_assert(M3_TILE_WORDS <= M3_THREADS, "one validity word per thread");
-    if (tid < M3_TILE_WORDS)
-        vm[tid] = (info & M3_SIMPLE) ? 0xffffffffu : m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, kv);
+    if (!full && tid < M3_TILE_WORDS) vm[tid] = m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, kv);
     for (uint32_t b = tid; b < B3; b += M3_THREADS) sm.cursor[b] = O1T[(size_t)b * pl.n_tiles + tile];
-    m3_clear_table(sm);
+    m3_clear_table2(sm);
     __syncthreads();
     const uint32_t pbase = (uint32_t)(w0 << 5) + w * M3_WARP_TILE + lane;
     // only the digit stays in registers; the code is formed again from the staged words when the record is staged
-    uint32_t dg[M3_ITEMS];
-#pragma unroll
-    for (int j = 0; j < M3_ITEMS; ++j) {
-        const int wi = w * M3_ITEMS + j;
-        dg[j] = ((vm[wi] >> lane) & 1u) ? (m3_code_at(words[wi], words[wi + 1], lane, k) >> sh3) : B3;
-    }
     const uint2 *wrow = words + w * M3_ITEMS;
-    m3_partition_tile<false, NBITS>(
-        sm, [&](int j) { return make_uint2(pbase + 32 * j, m3_code_at(wrow[j], wrow[j + 1], lane, k)); }, dg, (int)B3,
-        [sh3](uint32_t c) { return c >> sh3; }, out, nullptr);
+    uint32_t dg[M3_ITEMS];
+    auto rec = [&](int j) { return make_uint2(pbase + 32 * j, m3_code_at(wrow[j], wrow[j + 1], lane, k)); };
+    auto dig = [sh3](uint32_t c) { return c >> sh3; };
+    if (full) {
+#pragma unroll
+        for (int j = 0; j < M3_ITEMS; ++j) dg[j] = m3_code_at(wrow[j], wrow[j + 1], lane, k) >> sh3;
+        m3_partition_tile2<false, NBITS, true>(sm, rec, dg, (int)B3, dig, out, nullptr);
+    } else {
+#pragma unroll
+        for (int j = 0; j < M3_ITEMS; ++j)
+            dg[j] = ((vm[w * M3_ITEMS + j] >> lane) & 1u) ? (m3_code_at(wrow[j], wrow[j + 1], lane, k) >> sh3) : B3;
+        m3_partition_tile2<false, NBITS, false>(sm, rec, dg, (int)B3, dig, out, nullptr);
+    }
 }
 
 // ---- pass 2: range (chunk, d3) -> grouped by (d3, d2) --------------------------------------------
@@ -220,7 +225,7 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uin
                                                                  const uint32_t *__restrict__ base32,
                                                                  uint64_t *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char m3_raw[];
-    M3Smem &sm = *reinterpret_cast<M3Smem *>(m3_raw);
+    M3Smem2 &sm = *reinterpret_cast<M3Smem2 *>(m3_raw);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t B2 = 1u << pl.b2, B3 = 1u << pl.b3;
     const uint32_t c = blockIdx.x / B3, d3 = blockIdx.x % B3;
@@ -229,24 +234,34 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uin
                                                 : base32[(size_t)(d3 + 1) << pl.b2];
     if (begin >= end) return;
     for (uint32_t b = tid; b < B2; b += M3_THREADS) sm.cursor[b] = O2[(size_t)c * (B3 * B2) + ((size_t)d3 << pl.b2) + b];
-    m3_clear_table(sm);
+    m3_clear_table2(sm);
     __syncthreads();
     const int b1 = pl.b1;
     const uint32_t m2 = B2 - 1;
+    const uint32_t li0 = w * M3_WARP_TILE + lane;
+    auto dig = [b1, m2](uint32_t cd) { return (cd >> b1) & m2; };
     for (uint32_t t0 = begin; t0 < end; t0 += M3_TILE) {
-        const uint32_t tile_n = min((uint32_t)M3_TILE, end - t0);
-        const uint2 *src = in + t0 + w * M3_WARP_TILE + lane;
-        const uint32_t li0 = w * M3_WARP_TILE + lane;
+        const uint2 *src = in + t0 + li0;
         uint2 r[M3_ITEMS];
         uint32_t dg[M3_ITEMS];
+        if (end - t0 >= (uint32_t)M3_TILE) {        // full tile: straight-line loads, no sentinel
 #pragma unroll
-        for (int j = 0; j < M3_ITEMS; ++j) {
-            const bool ok = li0 + 32 * j < tile_n;
-            r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
-            dg[j] = ok ? ((r[j].y >> b1) & m2) : B2;
+            for (int j = 0; j < M3_ITEMS; ++j) r[j] = src[32 * j];
+#pragma unroll
+            for (int j = 0; j < M3_ITEMS; ++j) dg[j] = (r[j].y >> b1) & m2;
+            auto rec = [&](int j) { return r[j]; };
+            m3_partition_tile2<false, NBITS, true>(sm, rec, dg, (int)B2, dig, out, nullptr);
+        } else {
+            const uint32_t tile_n = end - t0;
+#pragma unroll
+            for (int j = 0; j < M3_ITEMS; ++j) {
+                const bool ok = li0 + 32 * j < tile_n;
+                r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
+                dg[j] = ok ? ((r[j].y >> b1) & m2) : B2;
+            }
+            auto rec = [&](int j) { return r[j]; };
+            m3_partition_tile2<false, NBITS, false>(sm, rec, dg, (int)B2, dig, out, nullptr);
         }
-        m3_partition_tile<false, NBITS>(sm, [&](int j) { return r[j]; }, dg, (int)B2,
-                                        [b1, m2](uint32_t cd) { return (cd >> b1) & m2; }, out, nullptr);
     }
 }
 
@@ -278,27 +293,30 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uin
                                                                  uint32_t *__restrict__ rowtab,
                                                                  uint32_t *__restrict__ out_pos) {
     extern __shared__ __align__(16) unsigned char m3_raw[];
-    M3Smem &sm = *reinterpret_cast<M3Smem *>(m3_raw);
+    M3Smem2 &sm = *reinterpret_cast<M3Smem2 *>(m3_raw);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t B1 = 1u << pl.b1, m1 = B1 - 1, cell = blockIdx.x;
     const uint32_t cells1 = (1u << (pl.b3 + pl.b2)) + 1;
     const uint32_t begin = base32[cell];
     // count d1 over the bucket (sm.delta doubles as the histogram)
     for (int b = tid; b < M3_MAX_BINS; b += M3_THREADS) sm.delta[b] = 0;
-    m3_clear_table(sm);
+    m3_clear_table2(sm);
     __syncthreads();
     for (uint32_t gi = 0; gi < n_groups; ++gi) {
         const uint32_t *gb = gbase + (size_t)gi * cells1;
         const uint32_t sb = goff[gi] + gb[cell], se = goff[gi] + gb[cell + 1];
-        // four loads in flight per thread: the bucket is read cold here (and again, from L2, below)
-        for (uint32_t i = sb + tid; i < se; i += M3_COUNT_UNROLL * M3_THREADS) {
+        // the bucket is read cold here (and again, from L2, below).  Whole blocks of M3_COUNT_UNROLL x M3_THREADS
+        // records run without a guard (round 1 paid a compare + branch around every one of the 8 loads: 13
+        // instructions per record round, SASS), the tail one record per thread and trip.
+        uint32_t i = sb + tid;
+        for (; i + (M3_COUNT_UNROLL - 1) * M3_THREADS < se; i += M3_COUNT_UNROLL * M3_THREADS) {
             uint32_t cd[M3_COUNT_UNROLL];
 #pragma unroll
-            for (int u = 0; u < M3_COUNT_UNROLL; ++u) cd[u] = i + u * M3_THREADS < se ? in[i + u * M3_THREADS].y : 0xffffffffu;
+            for (int u = 0; u < M3_COUNT_UNROLL; ++u) cd[u] = in[i + u * M3_THREADS].y;
 #pragma unroll
-            for (int u = 0; u < M3_COUNT_UNROLL; ++u)
-                if (cd[u] != 0xffffffffu) atomicAdd(&sm.delta[cd[u] & m1], 1u);
+            for (int u = 0; u < M3_COUNT_UNROLL; ++u) atomicAdd(&sm.delta[cd[u] & m1], 1u);
         }
+        for (; i < se; i += M3_THREADS) atomicAdd(&sm.delta[in[i].y & m1], 1u);
     }
     __syncthreads();
     {   // exclusive scan of the 256 counts -> first occurrence of every code of the bucket
@@ -330,23 +348,33 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uin
         }
     }
     __syncthreads();
+    const uint32_t li0 = w * M3_WARP_TILE + lane;
+    auto dig = [m1](uint32_t cd) { return cd & m1; };
     for (uint32_t gi = 0; gi < n_groups; ++gi) {
         const uint32_t *gb = gbase + (size_t)gi * cells1;
         const uint32_t sb = goff[gi] + gb[cell], se = goff[gi] + gb[cell + 1];
         for (uint32_t t0 = sb; t0 < se; t0 += M3_TILE) {
-            const uint32_t tile_n = min((uint32_t)M3_TILE, se - t0);
-            const uint2 *src = in + t0 + w * M3_WARP_TILE + lane;
-            const uint32_t li0 = w * M3_WARP_TILE + lane;
+            const uint2 *src = in + t0 + li0;
             uint2 r[M3_ITEMS];
             uint32_t dg[M3_ITEMS];
+            if (se - t0 >= (uint32_t)M3_TILE) {
 #pragma unroll
-            for (int j = 0; j < M3_ITEMS; ++j) {
-                const bool ok = li0 + 32 * j < tile_n;
-                r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
-                dg[j] = ok ? (r[j].y & m1) : B1;
+                for (int j = 0; j < M3_ITEMS; ++j) r[j] = src[32 * j];
+#pragma unroll
+                for (int j = 0; j < M3_ITEMS; ++j) dg[j] = r[j].y & m1;
+                auto rec = [&](int j) { return r[j]; };
+                m3_partition_tile2<true, NBITS, true>(sm, rec, dg, (int)B1, dig, nullptr, out_pos);
+            } else {
+                const uint32_t tile_n = se - t0;
+#pragma unroll
+                for (int j = 0; j < M3_ITEMS; ++j) {
+                    const bool ok = li0 + 32 * j < tile_n;
+                    r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
+                    dg[j] = ok ? (r[j].y & m1) : B1;
+                }
+                auto rec = [&](int j) { return r[j]; };
+                m3_partition_tile2<true, NBITS, false>(sm, rec, dg, (int)B1, dig, nullptr, out_pos);
             }
-            m3_partition_tile<true, NBITS>(sm, [&](int j) { return r[j]; }, dg, (int)B1,
-                                           [m1](uint32_t cd) { return cd & m1; }, nullptr, out_pos);
         }
     }
 }
@@ -415,9 +443,9 @@ void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_g
     g->m3_pos_lo = pos_lo;
     if (!(g->attr_mask & pdg_graph::ATTR_MSD3)) {
         PDG_CUDA(cudaFuncSetAttribute(m3_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 1 << 16));
-        PDG_CUDA(cudaFuncSetAttribute(m3_pass1_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
-        PDG_CUDA(cudaFuncSetAttribute(m3_pass2_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
-        PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem)));
+        PDG_CUDA(cudaFuncSetAttribute(m3_pass1_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem2)));
+        PDG_CUDA(cudaFuncSetAttribute(m3_pass2_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem2)));
+        PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem2)));
         g->attr_mask |= pdg_graph::ATTR_MSD3;
     }
 }
@@ -465,11 +493,11 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
     m3_scan_tiles_kernel<<<pl.n_chunks, 256, 0, s>>>(H1T, pl, H12, base32);
     PDG_LAUNCHED(g);
     mark(2);
-    m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem), s>>>(packed, pw, k, kv, ct, pl, tile_info, H1T,
+    m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem2), s>>>(packed, pw, k, kv, ct, pl, tile_info, H1T,
                                                                      g->recA.as<uint64_t>() + rec_off);
     PDG_LAUNCHED(g);
     mark(3);
-    m3_pass2_kernel<7><<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem), s>>>(g->recA.as<uint2>() + rec_off, pl, H1T, H12, base32,
+    m3_pass2_kernel<7><<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem2), s>>>(g->recA.as<uint2>() + rec_off, pl, H1T, H12, base32,
                                                                          g->recB.as<uint64_t>() + rec_off);
     PDG_LAUNCHED(g);
     mark(4);
@@ -501,7 +529,7 @@ void msd3_finish_launch(pdg_graph *g, bool rows) {
         m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32, nullptr, 0u);
         PDG_LAUNCHED(g);
     }
-    m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
+    m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem2), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
                                                               g->g_pos.as<uint32_t>());
     PDG_LAUNCHED(g);
     if (G == 1 && g->m3_timed)   // the group's other stages were timed

@@ -21,15 +21,6 @@ static constexpr int M3_TILE_WORDS = M3_TILE / 32;      // packed words per posi
 static constexpr int kMsd3MaxBits = 22;                 // k <= 11: digits (<=7, <=7, <=8)
 static constexpr uint32_t M3_SIMPLE = 0x80000000u;      // tile_info flag: every window is a k-mer
 
-// dynamic shared memory of one tile partition
-struct M3Smem {
-    uint2 stage[M3_TILE];                    // the tile in sorted order: {position, code}
-    uint32_t wcnt[M3_WARPS][M3_MAX_BINS];    // per (warp, bin): running count, then base inside the tile
-    uint32_t delta[M3_MAX_BINS];             // global offset of the bin's run minus its start in stage
-    uint32_t cursor[M3_MAX_BINS];            // global offset where this CTA writes the bin next
-    uint32_t wsum[M3_WARPS];
-};
-
 #ifdef __CUDACC__
 // k-mer code of position (32 * word + lane): hi / lo are the packed words `word` and `word + 1`
 // (big endian, 32 residues each).  Works on 32-bit halves: one funnel shift per window.
@@ -57,16 +48,14 @@ __device__ __forceinline__ uint32_t m3_valid_word(const ContigTable &ct, uint64_
     return m;
 }
 
-// Stable partition of one tile by a digit of NBITS bits.  Item j of lane l of warp w is tile
-// element w*32*M3_ITEMS + j*32 + l; dg[j] in [0, BINS) or BINS (= not a record, dropped; dg is clobbered).
-// rec(j) returns the record {position, code} of item j (called once, for kept items).  On entry sm.cursor[b] is the global offset of the first record
-// of bin b of this tile; on exit it has advanced by the tile's count (a CTA can walk consecutive
+// Stable partition of one tile by a digit of NBITS bits (m3_partition_tile2 below).  Item j of lane l of warp w is
+// tile element w*32*M3_ITEMS + j*32 + l; dg[j] in [0, BINS) or BINS (= not a record, dropped).  rec(j) returns the
+// record {position, code} of item j (called once, for kept items).  On entry sm.cursor[b] is the global offset of
+// the first record of bin b of this tile; on exit it has advanced by the tile's count (a CTA can walk consecutive
 // tiles of a range).  OUT4: write the position to out4, else (code << 32 | position) to out8.
-// Ranking: the lanes of a round that share a digit find each other with NBITS ballots (no shared
-// memory, no MATCH.ANY -- ~0.5 lanes/clk/SM on sm_100); the per-(warp, bin) running count is one
-// 32-bit word read by all and advanced by the lowest lane of the group.  ncu on the earlier
-// {mask, count} table ranked by a shared-memory atomicOr: 22 of 37 shared-memory wavefronts per 32
-// records went into ranking (ATOMS.OR alone 9); this form needs ~7.
+// Ranking: the lanes of a round that share a digit find each other with NBITS ballots (no shared memory, no
+// MATCH.ANY -- ~137 clk per warp instruction on B200, profiles/r02_pipelab.txt); the per-(warp, bin) running count is
+// one 32-bit word read by all and advanced by the lowest lane of the group.
 // Needs: wcnt zeroed and a barrier since; leaves wcnt zeroed and ends with a barrier.
 // One digit bit of the ranking ballots: lanes whose bit equals mine stay in `same` / never enter `other`.
 __device__ __forceinline__ void m3_vote_bit(uint32_t d, uint32_t bitmask, uint32_t &same, uint32_t &other) {
@@ -79,44 +68,69 @@ __device__ __forceinline__ void m3_vote_bit(uint32_t d, uint32_t bitmask, uint32
         : "+r"(same), "+r"(other) : "r"(d), "r"(bitmask));
 }
 
-template <bool OUT4, int NBITS, typename RecFn, typename DigitFn>
-__device__ __forceinline__ void m3_partition_tile(M3Smem &sm, RecFn rec, uint32_t (&dg)[M3_ITEMS],
-                                                  const int BINS, DigitFn digit, uint64_t *__restrict__ out8,
-                                                  uint32_t *__restrict__ out4) {
+// ---- v2 of the tile partition (round 2) ---------------------------------------------------------------------
+// Same algorithm and the same results as m3_partition_tile; what changed is the instruction count.  Measured on
+// B200 (tools/pipelab.cu, profiles/r02_pipelab.txt): one 7-bit ranking round costs ~26 clk per SMSP, i.e. only
+// ~0.35 ms of a 2.2-2.8 ms pass -- the passes were bound by the OTHER ~60-100 instructions per record round
+// (SASS of round 1: 92 per item in pass 2: ranking 52 of which ~30 needed, bin scan 14, scatter 9, write-out 16).
+//   * FULL = every item of the tile is a record: no validity ballot, no guards, no sentinel digit;
+//   * the (warp, bin) slot found while ranking is kept (packed with the rank) and reused by the scatter;
+//   * the bin scan is done by BINS threads only;
+//   * the write-out of a FULL tile is straight-line code (no per-item branch).
+// The count table stays row-major, wcnt[warp][bin] (bank = bin mod 32: the lanes of a warp spread over all banks).
+// A bin-major table would let the scan move a bin's 8 counts as two uint4, but then the lanes of one warp would
+// only ever touch 4 banks ((8 bin + warp) mod 32) in the ranking loop, the hottest one -- rejected on paper.
+struct M3Smem2 {
+    uint2 stage[M3_TILE];
+    uint32_t wcnt[M3_WARPS * M3_MAX_BINS];   // [warp][bin]: running count, then base inside the tile
+    uint32_t delta[M3_MAX_BINS];
+    uint32_t cursor[M3_MAX_BINS];
+    uint32_t wsum[M3_WARPS];
+};
+__device__ __forceinline__ void m3_clear_table2(M3Smem2 &sm) {
+    uint4 *t = reinterpret_cast<uint4 *>(sm.wcnt);
+#pragma unroll
+    for (int i = threadIdx.x; i < M3_WARPS * M3_MAX_BINS / 4; i += M3_THREADS) t[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
+template <bool OUT4, int NBITS, bool FULL, typename RecFn, typename DigitFn>
+__device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const uint32_t (&dg)[M3_ITEMS], const int BINS,
+                                                   DigitFn digit, uint64_t *__restrict__ out8,
+                                                   uint32_t *__restrict__ out4) {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t lt = (1u << lane) - 1u;
-    uint32_t *wc = sm.wcnt[w];
-    // ballots and the running count of the (warp, bin) pair, item by item; dg[j] becomes digit | rank << 16
-    // (ranking all items first and walking the counts afterwards cost ~10% more: the packed
-    // intermediate had to be unpacked again)
+    uint32_t pk[M3_ITEMS];      // slot in wcnt (low 16 bits) | rank inside the (warp, bin) run (high 16); ~0u = no record
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
-        const uint32_t d = dg[j], dd = d & (M3_MAX_BINS - 1);
-        const bool ok = d != (uint32_t)BINS;
-        uint32_t same = __ballot_sync(0xffffffffu, ok), other = 0u;
+        const uint32_t d = dg[j];
+        uint32_t same, other = 0u;
+        bool ok = true;
+        if (FULL) {
+            same = 0xffffffffu;
+        } else {
+            ok = d != (uint32_t)BINS;
+            same = __ballot_sync(0xffffffffu, ok);
+        }
 #pragma unroll
         for (int b = 0; b < NBITS; ++b) m3_vote_bit(d, 1u << b, same, other);
         const uint32_t peers = same & ~other, below = peers & lt;
-        const uint32_t cnt = wc[dd];
-        dg[j] = d | ((cnt + __popc(below)) << 16);
+        const uint32_t slot = w * M3_MAX_BINS + (FULL ? d : (d & (M3_MAX_BINS - 1)));
+        const uint32_t cnt = sm.wcnt[slot];
+        pk[j] = (FULL || ok) ? (slot | ((cnt + __popc(below)) << 16)) : 0xffffffffu;
         __syncwarp();
-        if (ok && below == 0u) wc[dd] = cnt + __popc(peers);
+        if ((FULL || ok) && below == 0u) sm.wcnt[slot] = cnt + __popc(peers);
         __syncwarp();
     }
     __syncthreads();
-    // bins tid*BPT .. tid*BPT+BPT-1: counts of the warps -> exclusive bases, tile count
-    uint32_t c[M3_BPT][M3_WARPS], tot[M3_BPT], sum = 0;
+    // bin tid (tid < BINS): the 8 per-warp counts -> exclusive bases; block scan over the bins
+    // (the 8 counts are NOT kept in registers across the barrier below: with 16 record registers and 8 packed ranks
+    // live that spilled 92-112 bytes per thread at 48 registers; they are read again when the bases are written)
+    uint32_t tot = 0;
+    if (tid < BINS) {
 #pragma unroll
-    for (int i = 0; i < M3_BPT; ++i) {
-        const int b = tid * M3_BPT + i;
-        tot[i] = 0;
-        if (b < BINS) {
-#pragma unroll
-            for (int ww = 0; ww < M3_WARPS; ++ww) { c[i][ww] = sm.wcnt[ww][b]; tot[i] += c[i][ww]; }
-        }
-        sum += tot[i];
+        for (int ww = 0; ww < M3_WARPS; ++ww) tot += sm.wcnt[ww * M3_MAX_BINS + tid];
     }
-    uint32_t inc = sum;
+    uint32_t inc = tot;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
@@ -124,47 +138,40 @@ __device__ __forceinline__ void m3_partition_tile(M3Smem &sm, RecFn rec, uint32_
     }
     if (lane == 31) sm.wsum[w] = inc;
     __syncthreads();
-    uint32_t base = 0, all = 0;
+    uint32_t all = M3_TILE;
+    {
+        const uint4 s0 = reinterpret_cast<const uint4 *>(sm.wsum)[0], s1 = reinterpret_cast<const uint4 *>(sm.wsum)[1];
+        const uint32_t v[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+        uint32_t base = 0, sum = 0;
 #pragma unroll
-    for (int ww = 0; ww < M3_WARPS; ++ww) {
-        const uint32_t v = sm.wsum[ww];
-        if (ww < w) base += v;
-        all += v;
-    }
-    uint32_t run = base + inc - sum;               // start of this thread's first bin inside the tile
+        for (int ww = 0; ww < M3_WARPS; ++ww) {
+            if (ww < w) base += v[ww];
+            sum += v[ww];
+        }
+        if (!FULL) all = sum;
+        if (tid < BINS) {
+            uint32_t run = base + inc - tot;            // start of bin tid inside the tile
+            const uint32_t cur = sm.cursor[tid];
+            sm.delta[tid] = cur - run;
+            sm.cursor[tid] = cur + tot;
 #pragma unroll
-    for (int i = 0; i < M3_BPT; ++i) {
-        const int b = tid * M3_BPT + i;
-        if (b < BINS) {
-            const uint32_t cur = sm.cursor[b];
-            sm.delta[b] = cur - run;
-            sm.cursor[b] = cur + tot[i];
-#ifdef M3_REREAD_COUNTS
-            // variant for tools/tune_msd3.py ("reread"): read the per-warp counts again instead of keeping them
-            // in registers across the scan (passes 2-3 spill them: 32 / 40 B of stack at 48 registers).
-            // Measured on B200 at 5e8 records, passes 1 / 2 / 3: 2.19 / 2.39 / 2.79 ms against 2.15 / 2.25 / 2.88
-            // -- helps pass 3 only, so it stays off until the choice is per pass.
-#pragma unroll
-            for (int ww = 0; ww < M3_WARPS; ++ww) { const uint32_t cw = sm.wcnt[ww][b]; sm.wcnt[ww][b] = run; run += cw; }
-#else
-#pragma unroll
-            for (int ww = 0; ww < M3_WARPS; ++ww) { sm.wcnt[ww][b] = run; run += c[i][ww]; }
-#endif
+            for (int ww = 0; ww < M3_WARPS; ++ww) {
+                const uint32_t cw = sm.wcnt[ww * M3_MAX_BINS + tid];
+                sm.wcnt[ww * M3_MAX_BINS + tid] = run;
+                run += cw;
+            }
         }
     }
     __syncthreads();
 #pragma unroll
-    for (int j = 0; j < M3_ITEMS; ++j) {
-        const uint32_t d = dg[j] & 0xffffu;
-        if (d != (uint32_t)BINS) sm.stage[wc[d] + (dg[j] >> 16)] = rec(j);
-    }
+    for (int j = 0; j < M3_ITEMS; ++j)
+        if (FULL || pk[j] != 0xffffffffu) sm.stage[sm.wcnt[pk[j] & 0xffffu] + (pk[j] >> 16)] = rec(j);
     __syncthreads();
-    // re-arm the table for the next tile while the stage drains
-    for (int i = tid; i < M3_WARPS * M3_MAX_BINS; i += M3_THREADS) (&sm.wcnt[0][0])[i] = 0u;
+    m3_clear_table2(sm);      // re-arm the table for the next tile while the stage drains
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const uint32_t s = j * M3_THREADS + tid;
-        if (s < all) {
+        if (FULL || s < all) {
             const uint2 x = sm.stage[s];
             const uint32_t at = sm.delta[digit(x.y)] + s;
             if (OUT4) out4[at] = x.x; else out8[at] = ((uint64_t)x.y << 32) | x.x;
@@ -173,9 +180,6 @@ __device__ __forceinline__ void m3_partition_tile(M3Smem &sm, RecFn rec, uint32_
     __syncthreads();
 }
 
-__device__ __forceinline__ void m3_clear_table(M3Smem &sm) {
-    for (int i = threadIdx.x; i < M3_WARPS * M3_MAX_BINS; i += M3_THREADS) (&sm.wcnt[0][0])[i] = 0u;
-}
 #endif
 
 }  // namespace pdg
