@@ -48,7 +48,7 @@
 extern "C" {
 #endif
 
-#define PDG_ABI_VERSION 5
+#define PDG_ABI_VERSION 6
 
 #define PDG_OK            0
 #define PDG_E_INVALID    -1   /* bad argument / bad state */
@@ -243,6 +243,23 @@ int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t
  * their node values can be opaque host strings, spell them with pdg_query_walk. */
 int pdg_query_strings_size(pdg_graph *g, uint64_t *total_bytes);
 int pdg_query_strings_fetch(pdg_graph *g, uint64_t *h_offsets, uint8_t *h_bytes);
+
+/* Graph.filter() (prairiedog/graph.py:62-63).  The one backend of the reference that implements it is NetworkXGraph
+ * (prairiedog/networkx_graph.py:53-75; LGGraph.filter is `pass`): on the UNDIRECTED SIMPLE graph of the node pairs
+ * -- one edge per pair whatever the labels, a self-loop counting twice in a degree -- remove the nodes with
+ * degree <= int(0.9 * max degree), then the nodes left without a neighbour.  Three calls so that the threshold is
+ * formed by the host exactly as the reference forms it (a Python float product truncated by int()):
+ *   pdg_filter_degrees  projects every labelled edge of the finalized graph onto that simple graph (pair keys over
+ *                       dense node ids, radix sort + dedup) and returns the maximum degree;
+ *   pdg_filter_select   applies both removals for the given bottom_degrees and returns how many nodes survive and how
+ *                       many labelled edges have both endpoints among them (the induced sub-multigraph);
+ *   pdg_filter_fetch    copies those labelled edges to host arrays of n_kept_edges entries and frees the working set.
+ * The graph itself is not modified: the caller rebuilds it from the fetched edges (B200Graph.filter does).
+ * Single-rank graphs only. */
+int pdg_filter_degrees(pdg_graph *g, uint32_t *max_degree);
+int pdg_filter_select(pdg_graph *g, uint32_t bottom_degrees, uint64_t *n_kept_nodes, uint64_t *n_kept_edges);
+int pdg_filter_fetch(pdg_graph *g, uint64_t *h_src_code, uint64_t *h_tgt_code, uint32_t *h_type_id,
+                     int32_t *h_value);
 
 /* K5: multi-GPU (one process per GPU).  The host exchanges the 128-byte id with torch.distributed.  Genomes shard
  * by sample and edges never move; inside pdg_finalize the ranks agree on the global node table: for k <= 15 one

@@ -67,7 +67,7 @@ class BuildStats(ctypes.Structure):
                 ("pad3", ctypes.c_float), ("sort_groups", c_u64), ("pipelined", c_u64), ("ingest_bytes", c_u64), ("ingest_launches", c_u64)]
 
 
-ABI_VERSION = 5      # PDG_ABI_VERSION of include/pdgpu.h
+ABI_VERSION = 6      # PDG_ABI_VERSION of include/pdgpu.h
 
 # name -> (restype, argtypes); every symbol of include/pdgpu.h (tests/test_abi.py checks the list
 # against the header)
@@ -103,6 +103,9 @@ SIGNATURES = {
     "pdg_query_paths": (c_int, [vp, vp, vp, c_u64, c_i64, u64p]),
     "pdg_query_fetch": (c_int, [vp, vp, vp]),
     "pdg_query_walk": (c_int, [vp, c_u64, ctypes.POINTER(Hit), vp, i32p]),
+    "pdg_filter_degrees": (c_int, [vp, ctypes.POINTER(ctypes.c_uint32)]),
+    "pdg_filter_select": (c_int, [vp, ctypes.c_uint32, u64p, u64p]),
+    "pdg_filter_fetch": (c_int, [vp, vp, vp, vp, vp]),
     "pdg_query_strings_size": (c_int, [vp, u64p]),
     "pdg_query_strings_fetch": (c_int, [vp, vp, vp]),
     "pdg_comm_unique_id": (c_int, [vp]),

@@ -413,7 +413,25 @@ class B200Graph(Graph):
         self._graph_labels.update(labels)
 
     def filter(self):
-        pass
+        """Graph.filter() (graph.py:62-63) as the one backend that implements it defines it
+        (networkx_graph.py:53-75; LGGraph.filter is `pass`): on the undirected simple graph of the node pairs, drop
+        the nodes of degree <= int(0.9 * max degree), then the isolates; the nodes go together with every labelled
+        edge that touches them.  Degrees, both removals and the surviving edge list are computed on the device
+        (pdg_filter_*); the graph is then rebuilt from the surviving labelled edges through the per-edge path, so
+        afterwards it holds exactly the induced sub-multigraph (committed)."""
+        if self._dist is not None:
+            raise NotImplementedError("filter() of a multi-rank graph: a node's edges are spread over the ranks")
+        self._publish()
+        if not self._published:
+            return
+        n_nodes, src, tgt, ty, val = self.engine.filter_edges()
+        self.engine.clear()            # the store goes too: what is left is explicit edges (labels stay on the host)
+        self._st_src, self._st_tgt, self._st_type, self._st_val, self._st_nodes = [], [], [], [], []
+        if src.size:
+            self.engine.add_edges(src, tgt, ty, val)
+        self.engine.finalize()
+        self._unsaved = False
+        self._published = True
 
     def __len__(self):
         self._publish()

@@ -113,6 +113,7 @@ int pdg_clear(pdg_graph *g) {
     g->g_kmers = g->g_edges = g->g_nodes = 0;
     g->x_n_nodes = g->x_n_edges = 0;
     g->q_n = g->q_total = 0;
+    g->flt_ready = g->flt_selected = false;
     g->launches = 0;
     return PDG_OK;
     PDG_API_END
@@ -411,6 +412,34 @@ int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits) {
 int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_node_codes, int32_t *status) {
     PDG_API_BEGIN
     return query_walk(g, src_code, hit, h_node_codes, status);
+    PDG_API_END
+}
+
+int pdg_filter_degrees(pdg_graph *g, uint32_t *max_degree) {
+    PDG_API_BEGIN
+    if (need_final(g, "pdg_filter_degrees")) return PDG_E_INVALID;
+    if (!max_degree) {
+        set_error("pdg_filter_degrees: null argument");
+        return PDG_E_INVALID;
+    }
+    return filter_degrees(g, max_degree);
+    PDG_API_END
+}
+
+int pdg_filter_select(pdg_graph *g, uint32_t bottom_degrees, uint64_t *n_kept_nodes, uint64_t *n_kept_edges) {
+    PDG_API_BEGIN
+    if (need_final(g, "pdg_filter_select")) return PDG_E_INVALID;
+    if (!n_kept_nodes || !n_kept_edges) {
+        set_error("pdg_filter_select: null argument");
+        return PDG_E_INVALID;
+    }
+    return filter_select(g, bottom_degrees, n_kept_nodes, n_kept_edges);
+    PDG_API_END
+}
+
+int pdg_filter_fetch(pdg_graph *g, uint64_t *h_src_code, uint64_t *h_tgt_code, uint32_t *h_type_id, int32_t *h_value) {
+    PDG_API_BEGIN
+    return filter_fetch(g, h_src_code, h_tgt_code, h_type_id, h_value);
     PDG_API_END
 }
 

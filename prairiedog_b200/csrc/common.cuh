@@ -172,6 +172,11 @@ struct pdg_graph {
     pdg::DevBuf qs_len, qs_off, qs_bytes;   // strings of the last query's hits (query.cu)
     uint64_t qs_total = 0;
     bool qs_ready = false;
+    // Graph.filter() working set (filter.cu), alive between pdg_filter_degrees and pdg_filter_fetch
+    pdg::DevBuf flt_src, flt_tgt, flt_type, flt_val, flt_uid, flt_vid, flt_adj, flt_deg;
+    pdg::DevBuf flt_osrc, flt_otgt, flt_otype, flt_oval;
+    uint64_t flt_pairs = 0, flt_kept_edges = 0;
+    bool flt_ready = false, flt_selected = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::vector<cudaEvent_t> k_events;   // per-kernel timing of msd3.cu / ingest_batch.cu
     bool collect_sort_stats = false;   // radix.cu times its pass kernels into stats
@@ -243,6 +248,11 @@ int query_run(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n
 int query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_codes, int32_t *status);
 int query_strings_size(pdg_graph *g, uint64_t *total_bytes);
 int query_strings_fetch(pdg_graph *g, uint64_t *h_offsets, uint8_t *h_bytes);
+
+// ---- filter.cu ----
+int filter_degrees(pdg_graph *g, uint32_t *max_degree);
+int filter_select(pdg_graph *g, uint32_t bottom_degrees, uint64_t *n_kept_nodes, uint64_t *n_kept_edges);
+int filter_fetch(pdg_graph *g, uint64_t *h_src, uint64_t *h_tgt, uint32_t *h_type, int32_t *h_val);
 
 // ---- comm.cu ----
 // in: sorted unique codes of this rank (d_local, n_local); out: g->u_codes_buf holds the global

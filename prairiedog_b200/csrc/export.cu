@@ -108,11 +108,12 @@ __global__ void checksum_nodes_kernel(const uint64_t *__restrict__ codes, uint64
     if ((threadIdx.x & 31) == 0 && h) atomicAdd(sum, h);
 }
 
-int export_edges(pdg_graph *g, uint64_t *h_src, uint64_t *h_tgt, uint32_t *h_type, int32_t *h_val) {
+// every labelled edge of the graph as device columns (src code, tgt code, type id, value): the genome part in index
+// order, then the explicit part in CSR order.  Shared by pdg_export_edges and the filter (filter.cu).
+int materialise_edges(pdg_graph *g, DevBuf &d_src, DevBuf &d_tgt, DevBuf &d_type, DevBuf &d_val) {
     cudaStream_t s = g->stream;
     const uint64_t ne = g->n_edges, ng = g->g_edges, nx = g->x_n_edges, nk = g->g_kmers;
     if (ne == 0) return PDG_OK;
-    DevBuf d_src, d_tgt, d_type, d_val;
     d_src.reserve(ne * 8, s); d_tgt.reserve(ne * 8, s); d_type.reserve(ne * 4, s); d_val.reserve(ne * 4, s);
     if (ng) {
         g->scratch0.reserve(nk * 4, s);
@@ -136,6 +137,16 @@ int export_edges(pdg_graph *g, uint64_t *h_src, uint64_t *h_tgt, uint32_t *h_typ
             d_tgt.as<uint64_t>() + ng, d_type.as<uint32_t>() + ng, d_val.as<int32_t>() + ng, nullptr);
         PDG_LAUNCHED(g);
     }
+    return PDG_OK;
+}
+
+int export_edges(pdg_graph *g, uint64_t *h_src, uint64_t *h_tgt, uint32_t *h_type, int32_t *h_val) {
+    cudaStream_t s = g->stream;
+    const uint64_t ne = g->n_edges;
+    if (ne == 0) return PDG_OK;
+    DevBuf d_src, d_tgt, d_type, d_val;
+    const int rc = materialise_edges(g, d_src, d_tgt, d_type, d_val);
+    if (rc != PDG_OK) return rc;
     if (h_src) PDG_CUDA(cudaMemcpyAsync(h_src, d_src.p, ne * 8, cudaMemcpyDeviceToHost, s));
     if (h_tgt) PDG_CUDA(cudaMemcpyAsync(h_tgt, d_tgt.p, ne * 8, cudaMemcpyDeviceToHost, s));
     if (h_type) PDG_CUDA(cudaMemcpyAsync(h_type, d_type.p, ne * 4, cudaMemcpyDeviceToHost, s));

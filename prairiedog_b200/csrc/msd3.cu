@@ -23,6 +23,7 @@ namespace pdg {
 struct M3Plan {
     int b1, b2, b3;              // digit widths, low to high
     uint32_t n_tiles, ch, n_chunks;
+    uint32_t n_chunks_cap;       // no sub-range of these positions plans more chunks than this (buffer sizing)
     uint64_t base0;              // first position of tile 0 (a multiple of 32)
 };
 
@@ -40,9 +41,11 @@ __global__ void m3_tile_info_kernel(ContigTable ct, M3Plan pl, int kv, uint32_t 
 
 // ---- histograms from the packed genome --------------------------------------------------------
 // H1T[d3][tile]; H12[chunk][d3 << b2 | d2]; tot32[cell] += chunk counts.
-// One CTA per chunk; every WARP takes whole tiles on its own (private d3 counters and validity
-// words), so there is no block barrier inside the tile loop.  Round i of a tile: lane l looks at
-// position 32*i + l, i.e. all lanes share the packed words i and i+1.
+// One CTA per chunk; every WARP takes whole tiles on its own (private d3 counters), so there is no block barrier
+// inside the tile loop.  A LANE owns one packed word (32 consecutive positions) and walks it from registers: the
+// window at position i of the word is one funnel shift by a compile-time amount of (word, top half of the next
+// word), its two digits one shift each.  (Round 1 walked the positions lane-parallel instead -- lane l = position
+// 32 i + l -- which cost three shuffles per round to broadcast word i: 30 instructions per 32 positions, 0.65 ms.)
 static constexpr int M3H_THREADS = 1024;
 static constexpr int M3H_WARPS = M3H_THREADS / 32;
 __global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const uint2 *__restrict__ packed, uint64_t packed_words,
@@ -52,10 +55,10 @@ __global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const uint2 *__res
                                                               unsigned int *__restrict__ tot32) {
     extern __shared__ uint32_t h12[];   // [cells]
     __shared__ uint32_t h1[M3H_WARPS][128];
-    __shared__ uint32_t vms[M3H_WARPS][M3_TILE_WORDS];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t cells = 1u << (pl.b3 + pl.b2), B3 = 1u << pl.b3;
-    const int sh2 = pl.b1, sh3 = pl.b1 + pl.b2;
+    // a window is the top 2k bits of a 32-bit funnel: its digits are plain right shifts of the funnel
+    const int sh2 = 32 - 2 * k + pl.b1, sh3 = 32 - 2 * k + pl.b1 + pl.b2;
     for (uint32_t i = tid; i < cells; i += M3H_THREADS) h12[i] = 0;
     __syncthreads();
     const uint32_t t0 = blockIdx.x * pl.ch, t1 = min(t0 + pl.ch, pl.n_tiles);
@@ -64,29 +67,29 @@ __global__ void __launch_bounds__(M3H_THREADS) m3_hist_kernel(const uint2 *__res
         const uint32_t info = tile_info[tile];
         for (int i = lane; i < 128; i += 32) h1[w][i] = 0;
         const bool simple = (info & M3_SIMPLE) != 0;
-        if (!simple)
-            for (int i = lane; i < M3_TILE_WORDS; i += 32) vms[w][i] = m3_valid_word(ct, w0 + i, info & ~M3_SIMPLE, kv);
         __syncwarp();
-        // lane l keeps packed words w0 + 32*g + l for the current group g of 32 rounds
+#pragma unroll 1
         for (int g = 0; g < M3_TILE_WORDS / 32; ++g) {
             const uint64_t wa = w0 + 32 * g + lane;
             const uint2 mine = wa < packed_words ? packed[wa] : make_uint2(0u, 0u);
-            const uint64_t wb = w0 + 32 * g + 32;
-            const uint2 next = (lane == 0 && wb < packed_words) ? packed[wb] : make_uint2(0u, 0u);
-#pragma unroll 8
-            for (int i = 0; i < 32; ++i) {
-                uint2 hi, lo;
-                hi.x = __shfl_sync(0xffffffffu, mine.x, i);
-                hi.y = __shfl_sync(0xffffffffu, mine.y, i);
-                // only the top half of the following word is ever needed (k <= 11)
-                const uint32_t nx = __shfl_sync(0xffffffffu, i == 31 ? next.y : mine.y, (i + 1) & 31);
-                lo.x = 0u;
-                lo.y = nx;
-                const uint32_t code = m3_code_at(hi, lo, lane, k);
-                const bool ok = simple || ((vms[w][32 * g + i] >> lane) & 1u);
-                if (ok) {
-                    atomicAdd(&h1[w][code >> sh3], 1u);
-                    atomicAdd(&h12[code >> sh2], 1u);
+            // only the top half of the following word is ever needed (k <= 11 <= 16 residues)
+            const uint32_t nxt = wa + 1 < packed_words ? packed[wa + 1].y : 0u;
+            if (simple) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const uint32_t f = i < 16 ? __funnelshift_l(mine.x, mine.y, 2 * i) : __funnelshift_l(nxt, mine.x, 2 * (i - 16));
+                    atomicAdd(&h1[w][f >> sh3], 1u);
+                    atomicAdd(&h12[f >> sh2], 1u);
+                }
+            } else {
+                const uint32_t vmask = m3_valid_word(ct, wa, info & ~M3_SIMPLE, kv);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const uint32_t f = i < 16 ? __funnelshift_l(mine.x, mine.y, 2 * i) : __funnelshift_l(nxt, mine.x, 2 * (i - 16));
+                    if ((vmask >> i) & 1u) {
+                        atomicAdd(&h1[w][f >> sh3], 1u);
+                        atomicAdd(&h12[f >> sh2], 1u);
+                    }
                 }
             }
         }
@@ -176,6 +179,12 @@ __global__ void __launch_bounds__(256) m3_scan_chunks_kernel(uint32_t *__restric
 
 // ---- pass 1: position tile -> records grouped by d3 ---------------------------------------------
 // FULL tile = every window of the tile is a k-mer (tile_info's M3_SIMPLE): no validity words, no guards.
+// A CTA walks M3_P1_TILES consecutive tiles: in pass 1's output the records of a digit are ordered by position, so
+// the run of (tile + 1, d3) starts where the run of (tile, d3) ends and the cursor the core advances is already right
+// -- the 128 scattered words of O1T (one per digit, n_tiles words apart) are fetched once per CTA, not once per tile.
+#ifndef M3_P1_TILES
+#define M3_P1_TILES 4
+#endif
 template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uint2 *__restrict__ packed,
                                                                  uint64_t packed_words, int k, int kv, ContigTable ct, M3Plan pl,
@@ -187,33 +196,37 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uin
     __shared__ uint2 words[M3_TILE_WORDS + 2];
     __shared__ uint32_t vm[M3_TILE_WORDS];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const uint32_t tile = blockIdx.x, B3 = 1u << pl.b3;
+    const uint32_t tile0 = blockIdx.x * M3_P1_TILES, tile1 = min(tile0 + (uint32_t)M3_P1_TILES, pl.n_tiles);
+    const uint32_t B3 = 1u << pl.b3;
     const int sh3 = pl.b1 + pl.b2;
-    const uint64_t w0 = (pl.base0 >> 5) + (uint64_t)tile * M3_TILE_WORDS;
-    const uint32_t info = tile_info[tile];
-    const bool full = (info & M3_SIMPLE) != 0;          // the same for the whole CTA
-    for (int i = tid; i < M3_TILE_WORDS + 2; i += M3_THREADS)
-        words[i] = w0 + i < packed_words ? packed[w0 + i] : make_uint2(0u, 0u);
-    static_assert(M3_TILE_WORDS <= M3_THREADS, "one validity word per thread");
-    if (!full && tid < M3_TILE_WORDS) vm[tid] = m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, kv);
-    for (uint32_t b = tid; b < B3; b += M3_THREADS) sm.cursor[b] = O1T[(size_t)b * pl.n_tiles + tile];
+    for (uint32_t b = tid; b < B3; b += M3_THREADS) sm.cursor[b] = O1T[(size_t)b * pl.n_tiles + tile0];
     m3_clear_table2(sm);
-    __syncthreads();
-    const uint32_t pbase = (uint32_t)(w0 << 5) + w * M3_WARP_TILE + lane;
-    // only the digit stays in registers; the code is formed again from the staged words when the record is staged
     const uint2 *wrow = words + w * M3_ITEMS;
-    uint32_t dg[M3_ITEMS];
-    auto rec = [&](int j) { return make_uint2(pbase + 32 * j, m3_code_at(wrow[j], wrow[j + 1], lane, k)); };
     auto dig = [sh3](uint32_t c) { return c >> sh3; };
-    if (full) {
+    static_assert(M3_TILE_WORDS <= M3_THREADS, "one validity word per thread");
+    for (uint32_t tile = tile0; tile < tile1; ++tile) {
+        const uint64_t w0 = (pl.base0 >> 5) + (uint64_t)tile * M3_TILE_WORDS;
+        const uint32_t info = tile_info[tile];
+        const bool full = (info & M3_SIMPLE) != 0;          // the same for the whole CTA
+        // (the previous tile's partition ended with a barrier: nobody reads words / vm any more)
+        for (int i = tid; i < M3_TILE_WORDS + 2; i += M3_THREADS)
+            words[i] = w0 + i < packed_words ? packed[w0 + i] : make_uint2(0u, 0u);
+        if (!full && tid < M3_TILE_WORDS) vm[tid] = m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, kv);
+        __syncthreads();
+        const uint32_t pbase = (uint32_t)(w0 << 5) + w * M3_WARP_TILE + lane;
+        // only the digit stays in registers; the code is formed again from the staged words when the record is staged
+        uint32_t dg[M3_ITEMS];
+        auto rec = [&](int j) { return make_uint2(pbase + 32 * j, m3_code_at(wrow[j], wrow[j + 1], lane, k)); };
+        if (full) {
 #pragma unroll
-        for (int j = 0; j < M3_ITEMS; ++j) dg[j] = m3_code_at(wrow[j], wrow[j + 1], lane, k) >> sh3;
-        m3_partition_tile2<false, NBITS, true>(sm, rec, dg, (int)B3, dig, out, nullptr);
-    } else {
+            for (int j = 0; j < M3_ITEMS; ++j) dg[j] = m3_code_at(wrow[j], wrow[j + 1], lane, k) >> sh3;
+            m3_partition_tile2<false, NBITS, true>(sm, rec, dg, (int)B3, dig, out, nullptr);
+        } else {
 #pragma unroll
-        for (int j = 0; j < M3_ITEMS; ++j)
-            dg[j] = ((vm[w * M3_ITEMS + j] >> lane) & 1u) ? (m3_code_at(wrow[j], wrow[j + 1], lane, k) >> sh3) : B3;
-        m3_partition_tile2<false, NBITS, false>(sm, rec, dg, (int)B3, dig, out, nullptr);
+            for (int j = 0; j < M3_ITEMS; ++j)
+                dg[j] = ((vm[w * M3_ITEMS + j] >> lane) & 1u) ? (m3_code_at(wrow[j], wrow[j + 1], lane, k) >> sh3) : B3;
+            m3_partition_tile2<false, NBITS, false>(sm, rec, dg, (int)B3, dig, out, nullptr);
+        }
     }
 }
 
@@ -417,6 +430,15 @@ static M3Plan m3_plan(int k, uint64_t pos0, uint64_t pos1) {
     static const uint32_t m3_min_chunks = getenv("PDG_M3_MIN_CHUNKS") ? (uint32_t)atoi(getenv("PDG_M3_MIN_CHUNKS")) : 148u;
     pl.ch = std::max<uint32_t>(1, std::min<uint32_t>(pl.ch, (pl.n_tiles + m3_min_chunks - 1) / m3_min_chunks));
     pl.n_chunks = (pl.n_tiles + pl.ch - 1) / pl.ch;
+    // the histogram kernel runs one 1024-thread CTA per chunk, two per SM: a chunk count just above a multiple of
+    // 2 x 148 leaves the last wave nearly empty (651 chunks at config 3 = 2.2 waves), so round it to whole waves
+    const uint32_t wave = 2 * 148;
+    pl.n_chunks_cap = std::max<uint32_t>(pl.n_chunks, wave) + wave;   // before / after rounding, whole or part of the range
+    if (pl.n_chunks > wave) {
+        const uint32_t waves = std::max<uint32_t>(1, (pl.n_chunks + wave / 2) / wave);
+        pl.ch = (pl.n_tiles + waves * wave - 1) / (waves * wave);
+        pl.n_chunks = (pl.n_tiles + pl.ch - 1) / pl.ch;
+    }
     return pl;
 }
 
@@ -429,7 +451,7 @@ void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_g
     const uint64_t n_codes = 1ULL << (2 * k), n = pos_hi - pos_lo;
     // a group never has more tiles / chunks than the whole range (+1 for its own alignment)
     g->status.reserve((size_t)B3 * (pl.n_tiles + 1) * 4, s);                                          // H1T -> O1T
-    g->scratch1.reserve(std::max<size_t>((size_t)(pl.n_chunks + 1) * cells * 4, (n_codes + 1) * 4), s);   // H12 -> O2, later ranks
+    g->scratch1.reserve(std::max<size_t>((size_t)(pl.n_chunks_cap + 1) * cells * 4, (n_codes + 1) * 4), s);   // H12 -> O2, later ranks
     g->hist.reserve((size_t)(2 * cells + 2) * 4, s);                                                  // tot32 | base32
     g->scratch0.reserve((n_codes + 1) * 4, s);                                                        // row starts of every code
     g->recA.reserve(std::max<size_t>(n * 8, n_codes * 4), s);
@@ -493,7 +515,7 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
     m3_scan_tiles_kernel<<<pl.n_chunks, 256, 0, s>>>(H1T, pl, H12, base32);
     PDG_LAUNCHED(g);
     mark(2);
-    m3_pass1_kernel<7><<<pl.n_tiles, M3_THREADS, sizeof(M3Smem2), s>>>(packed, pw, k, kv, ct, pl, tile_info, H1T,
+    m3_pass1_kernel<7><<<(pl.n_tiles + M3_P1_TILES - 1) / M3_P1_TILES, M3_THREADS, sizeof(M3Smem2), s>>>(packed, pw, k, kv, ct, pl, tile_info, H1T,
                                                                      g->recA.as<uint64_t>() + rec_off);
     PDG_LAUNCHED(g);
     mark(3);

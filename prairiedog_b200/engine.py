@@ -245,6 +245,22 @@ class Engine(object):
         check(self.lib.pdg_query_strings_fetch(self.h, off.ctypes.data, buf.data_ptr() if tot.value else None))
         return off, buf.numpy()[:tot.value]
 
+    # ---- Graph.filter() ----
+    def filter_edges(self, bottom_percentile=0.9):
+        """networkx_graph.py:53-75 on the device: (n_kept_nodes, src, tgt, type, value) of the labelled edges between
+        the nodes that survive the degree filter and the isolate filter.  The threshold is the reference's own
+        expression, int(bottom_percentile * max_degrees), evaluated here in Python."""
+        md = ctypes.c_uint32()
+        check(self.lib.pdg_filter_degrees(self.h, ctypes.byref(md)))
+        bottom_degrees = int(bottom_percentile * md.value)              # networkx_graph.py:60
+        nn, ne = ctypes.c_uint64(), ctypes.c_uint64()
+        check(self.lib.pdg_filter_select(self.h, bottom_degrees, ctypes.byref(nn), ctypes.byref(ne)))
+        n = ne.value
+        src, tgt = np.zeros(n, dtype=np.uint64), np.zeros(n, dtype=np.uint64)
+        ty, val = np.zeros(n, dtype=np.uint32), np.zeros(n, dtype=np.int32)
+        check(self.lib.pdg_filter_fetch(self.h, src.ctypes.data, tgt.ctypes.data, ty.ctypes.data, val.ctypes.data))
+        return nn.value, src, tgt, ty, val
+
     # ---- multi GPU ----
     def comm_unique_id(self):
         buf = np.zeros(128, dtype=np.uint8)

@@ -24,7 +24,7 @@ def test_library_exports_header_symbols(lib_built):
         assert hasattr(lib, n), n
     assert sorted(_ffi.SIGNATURES) == names
     lib.pdg_abi_version.restype = ctypes.c_int
-    assert lib.pdg_abi_version() == 5
+    assert lib.pdg_abi_version() == 6
 
 
 def test_struct_layouts(lib_built):

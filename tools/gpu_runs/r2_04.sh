@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, call 4 (1 GPU): v2 partition core -- GPU tests, A/B against the round-1 core and register budgets, bench
+# round 2, call 4 (1 GPU): partition core v2/v3, transposed histogram, filter() -- GPU tests, A/B of the variants, bench
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/r2_04_pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/r2_04_pytest.log
 timeout 900 python tools/tune_msd3.py --run 100 > gpurun_out/r2_04_tune.log 2>&1; echo "exit $?" >> gpurun_out/r2_04_tune.log
