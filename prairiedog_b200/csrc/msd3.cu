@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(256) m3_scan_chunks_kernel(uint32_t *__restric
 // the run of (tile + 1, d3) starts where the run of (tile, d3) ends and the cursor the core advances is already right
 // -- the 128 scattered words of O1T (one per digit, n_tiles words apart) are fetched once per CTA, not once per tile.
 #ifndef M3_P1_TILES
-#define M3_P1_TILES 4
+#define M3_P1_TILES 1   /* measured on B200: 1 tile 2.044 ms, 2: 2.096, 4: 2.069, 8: 2.075 -- the cursor loads were hidden anyway */
 #endif
 template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uint2 *__restrict__ packed,
@@ -430,15 +430,10 @@ static M3Plan m3_plan(int k, uint64_t pos0, uint64_t pos1) {
     static const uint32_t m3_min_chunks = getenv("PDG_M3_MIN_CHUNKS") ? (uint32_t)atoi(getenv("PDG_M3_MIN_CHUNKS")) : 148u;
     pl.ch = std::max<uint32_t>(1, std::min<uint32_t>(pl.ch, (pl.n_tiles + m3_min_chunks - 1) / m3_min_chunks));
     pl.n_chunks = (pl.n_tiles + pl.ch - 1) / pl.ch;
-    // the histogram kernel runs one 1024-thread CTA per chunk, two per SM: a chunk count just above a multiple of
-    // 2 x 148 leaves the last wave nearly empty (651 chunks at config 3 = 2.2 waves), so round it to whole waves
-    const uint32_t wave = 2 * 148;
-    pl.n_chunks_cap = std::max<uint32_t>(pl.n_chunks, wave) + wave;   // before / after rounding, whole or part of the range
-    if (pl.n_chunks > wave) {
-        const uint32_t waves = std::max<uint32_t>(1, (pl.n_chunks + wave / 2) / wave);
-        pl.ch = (pl.n_tiles + waves * wave - 1) / (waves * wave);
-        pl.n_chunks = (pl.n_tiles + pl.ch - 1) / pl.ch;
-    }
+    // (Rounding the chunk count to whole waves of the histogram kernel -- 651 -> 592 chunks at config 3 -- was tried:
+    // pass-2 ranges grew from 2.9 to 3.2 tiles, i.e. a nearly empty fourth tile each, 2.32 -> 2.47 ms.  The fit of a
+    // range to whole tiles matters more than the histogram's last wave; profiles/r02_tune_core_v2_v3.txt.)
+    pl.n_chunks_cap = pl.n_chunks + 1;
     return pl;
 }
 
