@@ -17,13 +17,9 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "v3": (256, 8, 5),                       # the product configuration
-    "v3_p1t1": (256, 8, 5, "-DM3_P1_TILES=1"),    # pass 1: tiles a CTA walks (product: 4)
-    "v3_p1t2": (256, 8, 5, "-DM3_P1_TILES=2"),
-    "v3_p1t8": (256, 8, 5, "-DM3_P1_TILES=8"),
-    "v3_b4": (256, 8, 4),                    # 64 registers: no spills, 32 warps per SM
-    "v3_b6": (256, 8, 6),                    # 40 registers: 48 warps per SM
-    "v2": (256, 8, 5, "src:60a2156"),        # v2 core, round-1 histogram kernel, one tile per pass-1 CTA
+    "v4": (256, 8, 5),                       # the product configuration: byte-wide (warp, bin) counts
+    "v4_b4": (256, 8, 4),                    # 64 registers: no spills, 32 warps per SM
+    "v3core": (256, 8, 5, "src:1df39de"),    # 32-bit count table (v2/v3 core), transposed histogram, 1 tile per pass-1 CTA
     "r1core": (256, 8, 5, "src:fa473bf"),    # round 1's core (msd3.cu / msd3.cuh of that commit)
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
