@@ -110,6 +110,99 @@ __global__ void compact_keys_kernel(const uint64_t *__restrict__ keys, const uin
     if (i < n && flags[i]) out[pos[i]] = keys[i];
 }
 
+// ---- owner side: union of the W sorted runs it received ---------------------------------------------------
+// Every run is a slice of some rank's sorted duplicate-free table, so the owner's set is a MERGE, not a sort: a
+// tree of two-way merges (log2 W rounds, 16 bytes of traffic per key and round) replaces the 8-pass LSD radix sort of
+// round 1 (128 bytes per key whatever W).  Each CTA produces MG_TILE consecutive outputs of one pair: "merge path" --
+// the split of the two inputs at an output diagonal is found by binary search (co-rank), the CTA's two input pieces
+// are staged in shared memory, every thread finds its own split there and merges MG_ITEMS keys serially; the result
+// goes back through shared memory so that the global stores are coalesced.  Equal keys of different runs stay
+// adjacent and are removed by the run-length compaction that follows, as before.
+static constexpr int MG_THREADS = 256, MG_ITEMS = 8, MG_TILE = MG_THREADS * MG_ITEMS;
+
+// number of keys taken from a[0, na) among the first `diag` outputs of merge(a, b); ties take a first
+template <typename T>
+__device__ __forceinline__ uint32_t mg_corank(const T *a, uint32_t na, const T *b, uint32_t nb, uint32_t diag) {
+    uint32_t lo = diag > nb ? diag - nb : 0u, hi = diag < na ? diag : na;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (a[mid] <= b[diag - 1 - mid]) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+__device__ __forceinline__ uint64_t mg_corank64(const uint64_t *__restrict__ a, uint64_t na, const uint64_t *__restrict__ b,
+                                                uint64_t nb, uint64_t diag) {
+    uint64_t lo = diag > nb ? diag - nb : 0ull, hi = diag < na ? diag : na;
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        if (a[mid] <= b[diag - 1 - mid]) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(MG_THREADS) merge_pair_kernel(const uint64_t *__restrict__ a, uint64_t na,
+                                                                const uint64_t *__restrict__ b, uint64_t nb,
+                                                                uint64_t *__restrict__ out) {
+    __shared__ uint64_t sk[MG_TILE];              // the CTA's piece of a, then its piece of b (together the tile's outputs, <= MG_TILE); later the merged tile
+    __shared__ uint64_t s_split[2];
+    const uint64_t d0 = (uint64_t)blockIdx.x * MG_TILE, total = na + nb;
+    const uint64_t d1 = d0 + MG_TILE < total ? d0 + MG_TILE : total;
+    if (threadIdx.x < 2) s_split[threadIdx.x] = mg_corank64(a, na, b, nb, threadIdx.x ? d1 : d0);
+    __syncthreads();
+    const uint64_t a0 = s_split[0], a1 = s_split[1], b0 = d0 - a0, b1 = d1 - a1;
+    const uint32_t la = (uint32_t)(a1 - a0), lb = (uint32_t)(b1 - b0), n = la + lb;
+    uint64_t *sa = sk, *sb = sk + la;
+    for (uint32_t i = threadIdx.x; i < la; i += MG_THREADS) sa[i] = a[a0 + i];
+    for (uint32_t i = threadIdx.x; i < lb; i += MG_THREADS) sb[i] = b[b0 + i];
+    __syncthreads();
+    const uint32_t t0 = min((uint32_t)threadIdx.x * MG_ITEMS, n), t1 = min(t0 + MG_ITEMS, n);
+    uint32_t ia = mg_corank(sa, la, sb, lb, t0), ib = t0 - ia;
+    uint64_t r[MG_ITEMS];
+#pragma unroll
+    for (int i = 0; i < MG_ITEMS; ++i) {
+        const bool have_a = ia < la, have_b = ib < lb;
+        const uint64_t ka = have_a ? sa[ia] : ~0ull, kb = have_b ? sb[ib] : ~0ull;
+        const bool take_a = have_a && (!have_b || ka <= kb);
+        r[i] = take_a ? ka : kb;
+        if (t0 + i < t1) { if (take_a) ++ia; else ++ib; }
+    }
+    __syncthreads();                               // every thread has read its inputs: the buffer becomes the output tile
+#pragma unroll
+    for (int i = 0; i < MG_ITEMS; ++i)
+        if (t0 + i < t1) sk[t0 + i] = r[i];
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n; i += MG_THREADS) out[d0 + i] = sk[i];
+}
+
+// Merges the sorted runs [off[p], off[p + 1]) of `src` (p = 0..W-1) into one sorted array; `tmp` has the same size.
+// Returns the buffer that holds the result (duplicates between runs are kept, adjacent).
+static uint64_t *merge_sorted_runs(pdg_graph *g, uint64_t *src, uint64_t *tmp, std::vector<uint64_t> off) {
+    cudaStream_t s = g->stream;
+    uint64_t *cur = src, *oth = tmp;
+    while (off.size() > 2) {
+        std::vector<uint64_t> next;
+        next.push_back(off[0]);
+        size_t p = 0;
+        for (; p + 2 < off.size(); p += 2) {
+            const uint64_t na = off[p + 1] - off[p], nb = off[p + 2] - off[p + 1];
+            if (na + nb) {
+                merge_pair_kernel<<<(unsigned)((na + nb + MG_TILE - 1) / MG_TILE), MG_THREADS, 0, s>>>(
+                    cur + off[p], na, cur + off[p + 1], nb, oth + off[p]);
+                PDG_LAUNCHED(g);
+            }
+            next.push_back(off[p + 2]);
+        }
+        if (p + 1 < off.size()) {          // an odd run is carried over as it is
+            const uint64_t nl = off[p + 1] - off[p];
+            if (nl) PDG_CUDA(cudaMemcpyAsync(oth + off[p], cur + off[p], nl * 8, cudaMemcpyDeviceToDevice, s));
+            next.push_back(off[p + 1]);
+        }
+        off.swap(next);
+        std::swap(cur, oth);
+    }
+    return cur;
+}
+
 static inline unsigned gridf(uint64_t n) { return (unsigned)((n + 255) / 256); }
 
 // Small k (every rank holds a presence bitmap over all 4^k codes and no explicit nodes): the global
@@ -229,14 +322,16 @@ int comm_global_nodes(pdg_graph *g, const uint64_t *d_local, uint64_t n_loc, int
     }
     PDG_NCCL(api, api->GroupEnd());
 
-    // 3. owner: sort + run-length compaction of what was received (W sorted runs of one key range)
+    // 3. owner: merge + run-length compaction of what was received (W sorted runs of one key range)
     uint64_t n_own = 0;
     DevBuf &d_own = g->c_own, &d_tmp = g->c_tmp;
     d_own.reserve(std::max<size_t>(n_recv * 8, 16), s);
     if (n_recv) {
         d_tmp.reserve(n_recv * 8, s);
+        static const bool lsd = getenv("PDG_EXCHANGE_LSD") != nullptr;     // round 1's owner-side radix sort, for A/B
         uint64_t pr = 0;
-        uint64_t *sorted = radix_sort_keys(g, d_recv.as<uint64_t>(), d_tmp.as<uint64_t>(), n_recv, 0, key_bits, &pr);
+        uint64_t *sorted = lsd ? radix_sort_keys(g, d_recv.as<uint64_t>(), d_tmp.as<uint64_t>(), n_recv, 0, key_bits, &pr)
+                               : merge_sorted_runs(g, d_recv.as<uint64_t>(), d_tmp.as<uint64_t>(), recv_off);
         g->scratch0.reserve(n_recv * 4, s);
         g->scratch1.reserve((n_recv + 1) * 8, s);
         head_flags_keys_kernel<<<gridf(n_recv), 256, 0, s>>>(sorted, n_recv, g->scratch0.as<uint32_t>());

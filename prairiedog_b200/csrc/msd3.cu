@@ -299,7 +299,7 @@ __global__ void m3_cell_totals_kernel(const uint32_t *__restrict__ gbase, uint32
 #define M3_COUNT_UNROLL 8   /* loads in flight per thread in the count loop; 1, 2, 4: 2-8% slower on B200 */
 #endif
 template <int NBITS>
-__global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass3_kernel(const uint2 *__restrict__ in, M3Plan pl,
+__global__ void __launch_bounds__(M3_THREADS, M3_MINB3) m3_pass3_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ gbase,
                                                                  const uint32_t *__restrict__ goff, uint32_t n_groups,
                                                                  const uint32_t *__restrict__ base32,

@@ -12,7 +12,11 @@ namespace pdg {
 static constexpr int M3_THREADS = M3_CFG_THREADS;
 static constexpr int M3_WARPS = M3_THREADS / 32;
 static constexpr int M3_ITEMS = M3_CFG_ITEMS;
-static constexpr int M3_MINB = M3_CFG_MINB;                       // CTAs per SM the pass kernels are compiled for
+static constexpr int M3_MINB = M3_CFG_MINB;                       // CTAs per SM passes 1-2 are compiled for
+#ifndef M3_CFG_MINB3
+#define M3_CFG_MINB3 4   /* pass 3 is the one pass that spills at 48 registers: 4 CTAs/SM (64 registers) 2.69 ms, 5: 2.81 ms */
+#endif
+static constexpr int M3_MINB3 = M3_CFG_MINB3;
 static constexpr int M3_TILE = M3_THREADS * M3_ITEMS;   // items per tile
 static constexpr int M3_WARP_TILE = 32 * M3_ITEMS;      // consecutive items per warp
 static constexpr int M3_MAX_BINS = 256;
@@ -68,48 +72,42 @@ __device__ __forceinline__ void m3_vote_bit(uint32_t d, uint32_t bitmask, uint32
         : "+r"(same), "+r"(other) : "r"(d), "r"(bitmask));
 }
 
-// ---- the tile partition, round-2 form -----------------------------------------------------------------------------
-// Same algorithm and results as round 1's; two things were learnt on the B200 (profiles/r02_pipelab.txt,
-// profiles/r02_tune_core_v2_v3.txt) and shape this version:
-//  1. A 7-bit ranking round costs ~26 clk per SMSP: ~0.35 ms of a 2.2-2.8 ms pass.  Cutting the OTHER instructions
-//     (full-tile fast path without guards, the (warp, bin) slot carried from the ranking to the scatter, straight-line
-//     write-out: 72 instead of 92 SASS instructions per item in pass 2) changed nothing: 2.23 -> 2.32 ms.  The passes
-//     are NOT instruction bound.
-//  2. What ncu shows saturated is the shared-memory data pipe (LSU 77-82 %, ~14 bank-conflict wavefronts per record
-//     round): 32 lanes with random digits read and update a table of 128-256 32-bit words in 32 banks, i.e. 4-8 words
-//     per bank, ~3.4 wavefronts per access, three accesses per item (count read, count update, base read).
-// So the (warp, bin) running counts are BYTES here: 128 bins = 32 words = one word per bank, every access of a warp is
-// one wavefront whatever the digits (two lanes in one word is a broadcast for loads; byte stores of different lanes
-// into one word merge -- measured, r02_pipelab.txt).  A count can reach 256 only when all 256 items of a warp share
-// one digit: the wrapped byte is repaired from `full[warp]`, set in the last round.  Bases inside the tile (< 2048)
-// live in a 16-bit table.  The bin scan zeroes the counts it has read, so there is no separate clearing pass.
+// ---- v2 of the tile partition (round 2) ---------------------------------------------------------------------
+// Same algorithm and the same results as m3_partition_tile; what changed is the instruction count.  Measured on
+// B200 (tools/pipelab.cu, profiles/r02_pipelab.txt): one 7-bit ranking round costs ~26 clk per SMSP, i.e. only
+// ~0.35 ms of a 2.2-2.8 ms pass -- the passes were bound by the OTHER ~60-100 instructions per record round
+// (SASS of round 1: 92 per item in pass 2: ranking 52 of which ~30 needed, bin scan 14, scatter 9, write-out 16).
+//   * FULL = every item of the tile is a record: no validity ballot, no guards, no sentinel digit;
+//   * the (warp, bin) slot found while ranking is kept (packed with the rank) and reused by the scatter;
+//   * the bin scan is done by BINS threads only;
+//   * the write-out of a FULL tile is straight-line code (no per-item branch).
+// Measured on B200 at config 3 (profiles/r02_tune_core_v2_v3.txt, r02_tune_core_v4.txt): against round 1's core this
+// one executes 21 % fewer instructions per item and is NOT faster (pass 1 2.15 -> 2.04, pass 2 2.23 -> 2.32, pass 3
+// 2.80 -> 2.81 ms); a variant with the counts as bytes (one word per bank: no bank conflict on any count access) was
+// slower still (pass 2 2.53 ms).  Neither instruction issue nor count-table conflicts bound these passes.
+// The count table stays row-major, wcnt[warp][bin] (bank = bin mod 32: the lanes of a warp spread over all banks).
+// A bin-major table would let the scan move a bin's 8 counts as two uint4, but then the lanes of one warp would
+// only ever touch 4 banks ((8 bin + warp) mod 32) in the ranking loop, the hottest one -- rejected on paper.
 struct M3Smem2 {
     uint2 stage[M3_TILE];
-    uint16_t base16[M3_WARPS * M3_MAX_BINS];  // [warp][bin]: start of the (warp, bin) run inside the tile
-    uint8_t cnt8[M3_WARPS * M3_MAX_BINS];     // [warp][bin]: running count mod 256 while ranking, zero otherwise
-    uint32_t full[M3_WARPS];                  // bin whose count reached 256 in this tile, else ~0u
-    uint32_t any_full;                        // some full[] entry is set (the repair is a cold path)
+    uint32_t wcnt[M3_WARPS * M3_MAX_BINS];   // [warp][bin]: running count, then base inside the tile
     uint32_t delta[M3_MAX_BINS];
     uint32_t cursor[M3_MAX_BINS];
     uint32_t wsum[M3_WARPS];
 };
-
-// before the first tile of a CTA (later tiles leave the tables armed)
 __device__ __forceinline__ void m3_clear_table2(M3Smem2 &sm) {
-    uint4 *t = reinterpret_cast<uint4 *>(sm.cnt8);
-    for (int i = threadIdx.x; i < M3_WARPS * M3_MAX_BINS / 16; i += M3_THREADS) t[i] = make_uint4(0u, 0u, 0u, 0u);
-    if (threadIdx.x < M3_WARPS) sm.full[threadIdx.x] = 0xffffffffu;
-    if (threadIdx.x == 0) sm.any_full = 0u;
+    uint4 *t = reinterpret_cast<uint4 *>(sm.wcnt);
+#pragma unroll
+    for (int i = threadIdx.x; i < M3_WARPS * M3_MAX_BINS / 4; i += M3_THREADS) t[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 template <bool OUT4, int NBITS, bool FULL, typename RecFn, typename DigitFn>
 __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const uint32_t (&dg)[M3_ITEMS], const int BINS,
                                                    DigitFn digit, uint64_t *__restrict__ out8,
                                                    uint32_t *__restrict__ out4) {
-    static_assert(M3_ITEMS * 32 == 256, "a (warp, bin) count of a tile must fit 8 bits + the `full` repair");
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t lt = (1u << lane) - 1u;
-    uint32_t pk[M3_ITEMS];      // slot in the tables (low 16 bits) | rank inside the (warp, bin) run (high 16); ~0u = no record
+    uint32_t pk[M3_ITEMS];      // slot in wcnt (low 16 bits) | rank inside the (warp, bin) run (high 16); ~0u = no record
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const uint32_t d = dg[j];
@@ -125,31 +123,20 @@ __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const
         for (int b = 0; b < NBITS; ++b) m3_vote_bit(d, 1u << b, same, other);
         const uint32_t peers = same & ~other, below = peers & lt;
         const uint32_t slot = w * M3_MAX_BINS + (FULL ? d : (d & (M3_MAX_BINS - 1)));
-        const uint32_t cnt = sm.cnt8[slot];
+        const uint32_t cnt = sm.wcnt[slot];
         pk[j] = (FULL || ok) ? (slot | ((cnt + __popc(below)) << 16)) : 0xffffffffu;
         __syncwarp();
-        if ((FULL || ok) && below == 0u) {
-            const uint32_t upto = cnt + __popc(peers);
-            sm.cnt8[slot] = (uint8_t)upto;
-            if (j == M3_ITEMS - 1 && upto == 256u) {                   // all 256 items of the warp in one bin
-                sm.full[w] = d;
-                sm.any_full = 1u;
-            }
-        }
+        if ((FULL || ok) && below == 0u) sm.wcnt[slot] = cnt + __popc(peers);
         __syncwarp();
     }
     __syncthreads();
-    // bin tid (tid < BINS): the 8 per-warp counts -> tile count; block scan over the bins
-    // (the counts are not kept in registers across the barrier below -- with 16 record registers and 8 packed ranks
-    // live that spilled; they are read again, and zeroed, when the bases are written)
+    // bin tid (tid < BINS): the 8 per-warp counts -> exclusive bases; block scan over the bins
+    // (the 8 counts are NOT kept in registers across the barrier below: with 16 record registers and 8 packed ranks
+    // live that spilled 92-112 bytes per thread at 48 registers; they are read again when the bases are written)
     uint32_t tot = 0;
-    const bool repair = sm.any_full != 0u;      // the same for the whole CTA, almost never set
     if (tid < BINS) {
 #pragma unroll
-        for (int ww = 0; ww < M3_WARPS; ++ww) tot += sm.cnt8[ww * M3_MAX_BINS + tid];
-        if (repair)
-            for (int ww = 0; ww < M3_WARPS; ++ww)
-                if (sm.full[ww] == (uint32_t)tid) tot += 256u;
+        for (int ww = 0; ww < M3_WARPS; ++ww) tot += sm.wcnt[ww * M3_MAX_BINS + tid];
     }
     uint32_t inc = tot;
 #pragma unroll
@@ -177,23 +164,18 @@ __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const
             sm.cursor[tid] = cur + tot;
 #pragma unroll
             for (int ww = 0; ww < M3_WARPS; ++ww) {
-                uint32_t cw = sm.cnt8[ww * M3_MAX_BINS + tid];
-                if (repair && sm.full[ww] == (uint32_t)tid) cw += 256u;
-                sm.cnt8[ww * M3_MAX_BINS + tid] = 0;    // armed for the next tile
-                sm.base16[ww * M3_MAX_BINS + tid] = (uint16_t)run;
+                const uint32_t cw = sm.wcnt[ww * M3_MAX_BINS + tid];
+                sm.wcnt[ww * M3_MAX_BINS + tid] = run;
                 run += cw;
             }
         }
     }
     __syncthreads();
-    if (repair) {                                       // read for the last time before the barrier above
-        if (tid < M3_WARPS) sm.full[tid] = 0xffffffffu;
-        if (tid == 0) sm.any_full = 0u;
-    }
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j)
-        if (FULL || pk[j] != 0xffffffffu) sm.stage[(uint32_t)sm.base16[pk[j] & 0xffffu] + (pk[j] >> 16)] = rec(j);
+        if (FULL || pk[j] != 0xffffffffu) sm.stage[sm.wcnt[pk[j] & 0xffffu] + (pk[j] >> 16)] = rec(j);
     __syncthreads();
+    m3_clear_table2(sm);      // re-arm the table for the next tile while the stage drains
 #pragma unroll
     for (int j = 0; j < M3_ITEMS; ++j) {
         const uint32_t s = j * M3_THREADS + tid;
