@@ -231,6 +231,9 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uin
 }
 
 // ---- pass 2: range (chunk, d3) -> grouped by (d3, d2) --------------------------------------------
+// The tiles of a range are fetched by bulk asynchronous copies (tma.cuh) into `inbuf`, one tile ahead: the copy of
+// tile t + 1 is started by one thread as soon as every thread holds tile t in registers (after the ranking barrier)
+// and lands while tile t is scanned, scattered and written.
 template <int NBITS>
 __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uint2 *__restrict__ in, M3Plan pl,
                                                                  const uint32_t *__restrict__ O1T,
@@ -239,6 +242,8 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uin
                                                                  uint64_t *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char m3_raw[];
     M3Smem2 &sm = *reinterpret_cast<M3Smem2 *>(m3_raw);
+    __shared__ __align__(16) uint2 inbuf[M3_TILE + 2];
+    __shared__ __align__(8) unsigned long long bar;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t B2 = 1u << pl.b2, B3 = 1u << pl.b3;
     const uint32_t c = blockIdx.x / B3, d3 = blockIdx.x % B3;
@@ -246,6 +251,11 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uin
     const uint32_t end = (c + 1 < pl.n_chunks) ? O1T[(size_t)d3 * pl.n_tiles + (size_t)(c + 1) * pl.ch]
                                                 : base32[(size_t)(d3 + 1) << pl.b2];
     if (begin >= end) return;
+    if (tid == 0) {
+        tma_bar_init(&bar, 1);
+        const TmaSpan sp = tma_span8(in + begin, min((uint32_t)M3_TILE, end - begin));
+        tma_load(inbuf, sp.src, sp.bytes, &bar);
+    }
     for (uint32_t b = tid; b < B2; b += M3_THREADS) sm.cursor[b] = O2[(size_t)c * (B3 * B2) + ((size_t)d3 << pl.b2) + b];
     m3_clear_table2(sm);
     __syncthreads();
@@ -253,19 +263,30 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uin
     const uint32_t m2 = B2 - 1;
     const uint32_t li0 = w * M3_WARP_TILE + lane;
     auto dig = [b1, m2](uint32_t cd) { return (cd >> b1) & m2; };
+    uint32_t parity = 0;
     for (uint32_t t0 = begin; t0 < end; t0 += M3_TILE) {
-        const uint2 *src = in + t0 + li0;
+        const uint32_t tile_n = min((uint32_t)M3_TILE, end - t0);
+        const uint2 *src = inbuf + tma_span8(in + t0, tile_n).skip + li0;
+        // the next tile of the range, fetched while this one is processed
+        const uint32_t nt0 = t0 + M3_TILE;
+        auto prefetch = [&]() {
+            if (tid == 0 && nt0 < end) {
+                const TmaSpan sp = tma_span8(in + nt0, min((uint32_t)M3_TILE, end - nt0));
+                tma_load(inbuf, sp.src, sp.bytes, &bar);
+            }
+        };
         uint2 r[M3_ITEMS];
         uint32_t dg[M3_ITEMS];
-        if (end - t0 >= (uint32_t)M3_TILE) {        // full tile: straight-line loads, no sentinel
+        tma_bar_wait(&bar, parity);
+        parity ^= 1u;
+        if (tile_n == (uint32_t)M3_TILE) {          // full tile: straight-line loads, no sentinel
 #pragma unroll
             for (int j = 0; j < M3_ITEMS; ++j) r[j] = src[32 * j];
 #pragma unroll
             for (int j = 0; j < M3_ITEMS; ++j) dg[j] = (r[j].y >> b1) & m2;
             auto rec = [&](int j) { return r[j]; };
-            m3_partition_tile2<false, NBITS, true>(sm, rec, dg, (int)B2, dig, out, nullptr);
+            m3_partition_tile2<false, NBITS, true>(sm, rec, dg, (int)B2, dig, out, nullptr, prefetch);
         } else {
-            const uint32_t tile_n = end - t0;
 #pragma unroll
             for (int j = 0; j < M3_ITEMS; ++j) {
                 const bool ok = li0 + 32 * j < tile_n;
@@ -273,7 +294,7 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass2_kernel(const uin
                 dg[j] = ok ? ((r[j].y >> b1) & m2) : B2;
             }
             auto rec = [&](int j) { return r[j]; };
-            m3_partition_tile2<false, NBITS, false>(sm, rec, dg, (int)B2, dig, out, nullptr);
+            m3_partition_tile2<false, NBITS, false>(sm, rec, dg, (int)B2, dig, out, nullptr, prefetch);
         }
     }
 }
@@ -307,6 +328,8 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB3) m3_pass3_kernel(const ui
                                                                  uint32_t *__restrict__ out_pos) {
     extern __shared__ __align__(16) unsigned char m3_raw[];
     M3Smem2 &sm = *reinterpret_cast<M3Smem2 *>(m3_raw);
+    __shared__ __align__(16) uint2 inbuf[M3_TILE + 2];
+    __shared__ __align__(8) unsigned long long bar;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t B1 = 1u << pl.b1, m1 = B1 - 1, cell = blockIdx.x;
     const uint32_t cells1 = (1u << (pl.b3 + pl.b2)) + 1;
@@ -363,32 +386,67 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB3) m3_pass3_kernel(const ui
     __syncthreads();
     const uint32_t li0 = w * M3_WARP_TILE + lane;
     auto dig = [m1](uint32_t cd) { return cd & m1; };
-    for (uint32_t gi = 0; gi < n_groups; ++gi) {
-        const uint32_t *gb = gbase + (size_t)gi * cells1;
-        const uint32_t sb = goff[gi] + gb[cell], se = goff[gi] + gb[cell + 1];
-        for (uint32_t t0 = sb; t0 < se; t0 += M3_TILE) {
-            const uint2 *src = in + t0 + li0;
-            uint2 r[M3_ITEMS];
-            uint32_t dg[M3_ITEMS];
-            if (se - t0 >= (uint32_t)M3_TILE) {
-#pragma unroll
-                for (int j = 0; j < M3_ITEMS; ++j) r[j] = src[32 * j];
-#pragma unroll
-                for (int j = 0; j < M3_ITEMS; ++j) dg[j] = r[j].y & m1;
-                auto rec = [&](int j) { return r[j]; };
-                m3_partition_tile2<true, NBITS, true>(sm, rec, dg, (int)B1, dig, nullptr, out_pos);
-            } else {
-                const uint32_t tile_n = se - t0;
-#pragma unroll
-                for (int j = 0; j < M3_ITEMS; ++j) {
-                    const bool ok = li0 + 32 * j < tile_n;
-                    r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
-                    dg[j] = ok ? (r[j].y & m1) : B1;
-                }
-                auto rec = [&](int j) { return r[j]; };
-                m3_partition_tile2<true, NBITS, false>(sm, rec, dg, (int)B1, dig, nullptr, out_pos);
-            }
+    // The tiles of the bucket, segment after segment, fetched one ahead by bulk asynchronous copies (see pass 2).
+    // (gi, t0, se) = the current tile's group, first record and the end of its segment; every thread walks the same
+    // sequence, thread 0 issues the copies.
+    auto segment = [&](uint32_t g, uint32_t &b0, uint32_t &e0) {
+        const uint32_t *gb = gbase + (size_t)g * cells1;
+        b0 = goff[g] + gb[cell];
+        e0 = goff[g] + gb[cell + 1];
+    };
+    // first tile at or after (g, t) -- skips empty segments; false when the bucket is exhausted
+    auto settle = [&](uint32_t &g, uint32_t &t, uint32_t &e) {
+        while (g < n_groups) {
+            if (t < e) return true;
+            if (++g < n_groups) segment(g, t, e);
         }
+        return false;
+    };
+    uint32_t gi = 0, t0 = 0, se = 0;
+    if (n_groups) segment(0, t0, se);
+    bool have = settle(gi, t0, se);
+    if (tid == 0) {
+        tma_bar_init(&bar, 1);
+        if (have) {
+            const TmaSpan sp = tma_span8(in + t0, min((uint32_t)M3_TILE, se - t0));
+            tma_load(inbuf, sp.src, sp.bytes, &bar);
+        }
+    }
+    __syncthreads();
+    uint32_t parity = 0;
+    while (have) {
+        const uint32_t tile_n = min((uint32_t)M3_TILE, se - t0);
+        const uint2 *src = inbuf + tma_span8(in + t0, tile_n).skip + li0;
+        uint32_t ngi = gi, nt0 = t0 + M3_TILE, nse = se;
+        const bool nhave = settle(ngi, nt0, nse);
+        auto prefetch = [&]() {
+            if (tid == 0 && nhave) {
+                const TmaSpan sp = tma_span8(in + nt0, min((uint32_t)M3_TILE, nse - nt0));
+                tma_load(inbuf, sp.src, sp.bytes, &bar);
+            }
+        };
+        uint2 r[M3_ITEMS];
+        uint32_t dg[M3_ITEMS];
+        tma_bar_wait(&bar, parity);
+        parity ^= 1u;
+        if (tile_n == (uint32_t)M3_TILE) {
+#pragma unroll
+            for (int j = 0; j < M3_ITEMS; ++j) r[j] = src[32 * j];
+#pragma unroll
+            for (int j = 0; j < M3_ITEMS; ++j) dg[j] = r[j].y & m1;
+            auto rec = [&](int j) { return r[j]; };
+            m3_partition_tile2<true, NBITS, true>(sm, rec, dg, (int)B1, dig, nullptr, out_pos, prefetch);
+        } else {
+#pragma unroll
+            for (int j = 0; j < M3_ITEMS; ++j) {
+                const bool ok = li0 + 32 * j < tile_n;
+                r[j] = ok ? src[32 * j] : make_uint2(0u, 0u);
+                dg[j] = ok ? (r[j].y & m1) : B1;
+            }
+            auto rec = [&](int j) { return r[j]; };
+            m3_partition_tile2<true, NBITS, false>(sm, rec, dg, (int)B1, dig, nullptr, out_pos, prefetch);
+        }
+        gi = ngi; t0 = nt0; se = nse; have = nhave;
     }
 }
 
@@ -449,8 +507,9 @@ void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_g
     g->scratch1.reserve(std::max<size_t>((size_t)(pl.n_chunks_cap + 1) * cells * 4, (n_codes + 1) * 4), s);   // H12 -> O2, later ranks
     g->hist.reserve((size_t)(2 * cells + 2) * 4, s);                                                  // tot32 | base32
     g->scratch0.reserve((n_codes + 1) * 4, s);                                                        // row starts of every code
-    g->recA.reserve(std::max<size_t>(n * 8, n_codes * 4), s);
-    g->recB.reserve(std::max<size_t>(n * 8, 16), s);
+    // + 64: a bulk copy (tma.cuh) rounds its span to 16 bytes, i.e. reads up to one record past the last one
+    g->recA.reserve(std::max<size_t>(n * 8, n_codes * 4) + 64, s);
+    g->recB.reserve(std::max<size_t>(n * 8, 16) + 64, s);
     g->g_pos.reserve(std::max<size_t>(n * 4, 16), s);
     g->m3_tile_info.reserve((size_t)(pl.n_tiles + 1) * 4, s);
     g->m3_gbase.reserve((size_t)max_groups * (cells + 1) * 4 + (size_t)max_groups * 4, s);

@@ -1,6 +1,7 @@
 // msd3.cuh -- constants and the per-tile partition core of the offsets-first MSD sort (msd3.cu).
 #pragma once
 #include "traverse.cuh"
+#include "tma.cuh"
 
 namespace pdg {
 
@@ -101,10 +102,14 @@ __device__ __forceinline__ void m3_clear_table2(M3Smem2 &sm) {
     for (int i = threadIdx.x; i < M3_WARPS * M3_MAX_BINS / 4; i += M3_THREADS) t[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
-template <bool OUT4, int NBITS, bool FULL, typename RecFn, typename DigitFn>
+// after_rank(): called by every thread right after the barrier that ends the ranking -- the first point at which no
+// thread needs the tile's INPUT any more (the records are in registers); passes 2-3 start the copy of the next tile there
+struct M3NoHook { __device__ __forceinline__ void operator()() const {} };
+
+template <bool OUT4, int NBITS, bool FULL, typename RecFn, typename DigitFn, typename HookFn = M3NoHook>
 __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const uint32_t (&dg)[M3_ITEMS], const int BINS,
                                                    DigitFn digit, uint64_t *__restrict__ out8,
-                                                   uint32_t *__restrict__ out4) {
+                                                   uint32_t *__restrict__ out4, HookFn after_rank = HookFn()) {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t pk[M3_ITEMS];      // slot in wcnt (low 16 bits) | rank inside the (warp, bin) run (high 16); ~0u = no record
@@ -130,6 +135,7 @@ __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const
         __syncwarp();
     }
     __syncthreads();
+    after_rank();
     // bin tid (tid < BINS): the 8 per-warp counts -> exclusive bases; block scan over the bins
     // (the 8 counts are NOT kept in registers across the barrier below: with 16 record registers and 8 packed ranks
     // live that spilled 92-112 bytes per thread at 48 registers; they are read again when the bases are written)

@@ -17,9 +17,8 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "v4": (256, 8, 5),                       # the product configuration: byte-wide (warp, bin) counts
-    "v4_b4": (256, 8, 4),                    # 64 registers: no spills, 32 warps per SM
-    "v3core": (256, 8, 5, "src:1df39de"),    # 32-bit count table (v2/v3 core), transposed histogram, 1 tile per pass-1 CTA
+    "tma": (256, 8, 5),                      # the product: next tile of passes 2-3 prefetched by cp.async.bulk
+    "notma": (256, 8, 5, "src:b914e62"),     # the same core, tiles loaded by the threads themselves
     "r1core": (256, 8, 5, "src:fa473bf"),    # round 1's core (msd3.cu / msd3.cuh of that commit)
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
