@@ -228,6 +228,8 @@ int pdg_query_connected(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, 
                         uint64_t *total_starts);
 int pdg_query_paths(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint64_t n_q,
                     int64_t max_len, uint64_t *total_hits);
+/* pdg_query_fetch: either destination may also be DEVICE memory (a multi-rank caller exchanges the hits between the
+ * ranks without a host round trip); the call returns after the copies have completed. */
 int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits);
 int pdg_query_walk(pdg_graph *g, uint64_t src_code, const pdg_hit *hit, uint64_t *h_node_codes,
                    int32_t *status);

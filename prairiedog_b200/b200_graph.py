@@ -488,18 +488,30 @@ class B200Graph(Graph):
         keeps the answer of this rank's shard."""
         a = self._codes([p[0] for p in pairs])
         b = self._codes([p[1] for p in pairs])
-        if not self._published:
-            from .engine import HIT_DTYPE
-            off, hits = np.zeros(len(pairs) + 1, dtype=np.uint64), np.zeros(0, dtype=HIT_DTYPE)
-        else:
-            off, hits = self.engine.query_paths(a, b, self.path_limit if limit is None else limit)
+        lim = self.path_limit if limit is None else limit
         self.hit_owner = None
         if self._dist is not None and not local:
             from . import distributed
             rank, world, dev = self._dist
             if self._type_bases is None:
                 self._type_bases = distributed.type_bases(self._next_type, dev)
-            off, hits, self.hit_owner = distributed.exchange_hits(off, hits, int(self._type_bases[rank]), dev)
+            base = int(self._type_bases[rank])
+            if self._published and dev is not None and getattr(dev, "type", "") == "cuda":
+                # the hits stay on the device from the query kernels to the merged answer
+                off_t, hits_t = self.engine.query_paths_device(a, b, lim)
+                off, hits, self.hit_owner = distributed.exchange_hits_device(off_t, hits_t, base)
+                return a, off, hits
+            from .engine import HIT_DTYPE
+            if self._published:
+                off, hits = self.engine.query_paths(a, b, lim)
+            else:
+                off, hits = np.zeros(len(pairs) + 1, dtype=np.uint64), np.zeros(0, dtype=HIT_DTYPE)
+            off, hits, self.hit_owner = distributed.exchange_hits(off, hits, base, dev)
+            return a, off, hits
+        if not self._published:
+            from .engine import HIT_DTYPE
+            return a, np.zeros(len(pairs) + 1, dtype=np.uint64), np.zeros(0, dtype=HIT_DTYPE)
+        off, hits = self.engine.query_paths(a, b, lim)
         return a, off, hits
 
     def query_many(self, pairs, limit=None, strings=True):

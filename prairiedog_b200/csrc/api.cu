@@ -401,9 +401,11 @@ int pdg_query_paths(pdg_graph *g, const uint64_t *h_a, const uint64_t *h_b, uint
 int pdg_query_fetch(pdg_graph *g, uint64_t *h_offsets, pdg_hit *h_hits) {
     PDG_API_BEGIN
     cudaStream_t s = g->stream;
-    if (h_offsets) PDG_CUDA(cudaMemcpyAsync(h_offsets, g->q_off.p, (g->q_n + 1) * 8, cudaMemcpyDeviceToHost, s));
+    // cudaMemcpyDefault: the destinations may be host OR device memory (unified addressing tells them apart) -- a
+    // multi-rank caller keeps the hits on the device for the exchange between the ranks
+    if (h_offsets) PDG_CUDA(cudaMemcpyAsync(h_offsets, g->q_off.p, (g->q_n + 1) * 8, cudaMemcpyDefault, s));
     if (h_hits && g->q_total)
-        PDG_CUDA(cudaMemcpyAsync(h_hits, g->q_hits.p, g->q_total * sizeof(pdg_hit), cudaMemcpyDeviceToHost, s));
+        PDG_CUDA(cudaMemcpyAsync(h_hits, g->q_hits.p, g->q_total * sizeof(pdg_hit), cudaMemcpyDefault, s));
     PDG_CUDA(cudaStreamSynchronize(s));
     return PDG_OK;
     PDG_API_END

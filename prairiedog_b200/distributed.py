@@ -230,6 +230,50 @@ def exchange_hits(off, hits, type_base, device=None):
             owner.cpu().numpy())
 
 
+def exchange_hits_device(off_t, hits_t, type_base):
+    """exchange_hits for results that are already torch tensors on the rank's device (Engine.query_paths_device):
+    nothing crosses the host before the merged answer is copied out once, through a pinned buffer.  Collective.
+    off_t int64[n_q + 1], hits_t int32[n, 4] with LOCAL type ids in column 0."""
+    import torch
+    import torch.distributed as dist
+    from .engine import HIT_DTYPE
+    rank, world = _world()
+    dev = off_t.device
+    c = off_t[1:] - off_t[:-1]
+    mine = hits_t.clone()
+    if mine.shape[0]:
+        mine[:, 0] += int(type_base)          # type ids stay below 2^31: int32 arithmetic is exact
+    if world == 1:
+        counts, recv, totals = c[None, :], [mine], [int(mine.shape[0])]
+    else:
+        cs = [torch.empty_like(c) for _ in range(world)]
+        dist.all_gather(cs, c)
+        counts = torch.stack(cs)
+        totals = counts.sum(dim=1).cpu().tolist()
+        cap = max(int(max(totals)), 1)
+        send = torch.zeros((cap, 4), dtype=torch.int32, device=dev)
+        send[:mine.shape[0]] = mine
+        recv = [torch.empty_like(send) for _ in range(world)]
+        dist.all_gather(recv, send)
+    goff, ghits, owner = merge_hits_torch(counts, recv, totals)
+    n = int(ghits.shape[0])
+    if dev.type != "cuda":        # CPU tensors (the gloo tests): nothing to copy out
+        return (goff.numpy().astype(np.uint64), ghits.contiguous().numpy().reshape(-1).view(HIT_DTYPE).copy(),
+                owner.numpy())
+    # one copy out, into pinned memory kept between calls
+    global _PINNED_HITS
+    if _PINNED_HITS is None or _PINNED_HITS.shape[0] < n:
+        _PINNED_HITS = torch.empty((max(int(n * 1.25), 1 << 16), 4), dtype=torch.int32, pin_memory=True)
+    _PINNED_HITS[:n].copy_(ghits, non_blocking=True)
+    owner_h, goff_h = owner.cpu(), goff.cpu()
+    torch.cuda.synchronize(dev)
+    return (goff_h.numpy().astype(np.uint64), _PINNED_HITS[:n].numpy().reshape(-1).view(HIT_DTYPE).copy(),
+            owner_h.numpy())
+
+
+_PINNED_HITS = None
+
+
 def gather_objects(obj):
     """all_gather_object (strings of the hits a rank owns, type labels): list indexed by rank"""
     import torch.distributed as dist

@@ -210,6 +210,20 @@ class Engine(object):
         check(self.lib.pdg_query_fetch(self.h, off.ctypes.data, hits.ctypes.data if tot.value else None))
         return off, hits
 
+    def query_paths_device(self, a, b, max_len=-1):
+        """query_paths with the result left on the device: (offsets int64[n_q + 1], hits int32[n_hits, 4]) as torch
+        CUDA tensors (pdg_query_fetch into device memory) -- the multi-rank exchange starts from these."""
+        import torch
+        a, b = _u64(a), _u64(b)
+        tot = ctypes.c_uint64()
+        check(self.lib.pdg_query_paths(self.h, a.ctypes.data, b.ctypes.data, a.size, int(max_len), ctypes.byref(tot)))
+        self._last_hits = tot.value
+        dev = "cuda:%d" % self.device
+        off = torch.empty(a.size + 1, dtype=torch.int64, device=dev)
+        hits = torch.empty((max(tot.value, 1), 4), dtype=torch.int32, device=dev)
+        check(self.lib.pdg_query_fetch(self.h, off.data_ptr(), hits.data_ptr() if tot.value else None))
+        return off, hits[:tot.value]
+
     def query_connected(self, a, b):
         """(offsets[n_q+1], hits): one hit per start edge (type_id, i)."""
         return self._query(self.lib.pdg_query_connected, a, b)

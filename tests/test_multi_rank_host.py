@@ -125,6 +125,11 @@ def _query_worker(rank, world, port, k, out_dir):
             off.append(len(rows))
         local = np.array(rows, dtype=HIT_DTYPE) if rows else np.zeros(0, dtype=HIT_DTYPE)
         goff, ghits, owner = D.exchange_hits(np.array(off, dtype=np.uint64), local, int(bases[rank]))
+        # the all-on-device form of the same exchange (torch tensors in; CPU tensors over gloo here)
+        import torch
+        g2 = D.exchange_hits_device(torch.tensor(off, dtype=torch.int64),
+                                    torch.from_numpy(local.view(np.int32).reshape(-1, 4).copy()), int(bases[rank]))
+        assert g2[0].tolist() == goff.tolist() and np.array_equal(g2[1], ghits) and g2[2].tolist() == owner.tolist()
         # every rank receives the same global answer
         want_off, want = [0], []
         for a, b in zip(qa.tolist(), qb.tolist()):
@@ -161,6 +166,12 @@ def test_merge_hits_orders_by_pair_then_rank():
     assert owner.tolist() == [0, 0, 1, 1, 1, 0]
     off, hits, owner = D.merge_hits([[0, 0]], [np.zeros(0, dtype=HIT_DTYPE)])
     assert off.tolist() == [0, 0, 0] and hits.size == 0
+    # the all-on-device form (torch tensors in, here on the CPU) gives the same answer as the host form
+    import torch
+    want = D.exchange_hits(np.array([0, 2, 3], dtype=np.uint64), r0, 10)
+    got = D.exchange_hits_device(torch.tensor([0, 2, 3], dtype=torch.int64),
+                                 torch.from_numpy(r0.view(np.int32).reshape(-1, 4).copy()), 10)
+    assert got[0].tolist() == want[0].tolist() and np.array_equal(got[1], want[1]) and got[2].tolist() == want[2].tolist()
     # single process: exchange_hits only applies the type base
     off, hits, owner = D.exchange_hits(np.array([0, 2, 3], dtype=np.uint64), r0, 10)
     assert hits["type_id"].tolist() == [10, 10, 11] and off.tolist() == [0, 2, 3] and r0["type_id"].tolist() == [0, 0, 1]

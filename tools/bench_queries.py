@@ -173,8 +173,8 @@ def main():
     def run_global():
         if world == 1:
             return run_local()
-        off, hits = run_local()
-        goff, ghits, _ = D.exchange_hits(off, hits, int(g._type_bases[rank]), dev)
+        off_t, hits_t = g.engine.query_paths_device(qa, qb, limit)     # what B200Graph.path_many does at world > 1
+        goff, ghits, _ = D.exchange_hits_device(off_t, hits_t, int(g._type_bases[rank]))
         return goff, ghits
 
     if world > 1:
