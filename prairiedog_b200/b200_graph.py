@@ -484,8 +484,9 @@ class B200Graph(Graph):
         """Batched path(): (codes of the a's, offsets[n_pairs + 1], hit records {type_id, i, j, aux}) -- no Node
         objects are built.  In a multi-rank job (distributed.attach) the call is COLLECTIVE: every rank passes the
         same pairs, runs them against its own shard and receives the hits of the whole pangenome, type ids in the
-        global numbering (``self.hit_owner`` then names the rank that holds each hit's contig); ``local=True``
-        keeps the answer of this rank's shard."""
+        global numbering (``self.hit_owner`` then names the rank that holds each hit's contig; the returned
+        arrays are views of a pinned buffer that the next collective call reuses); ``local=True`` keeps the answer of
+        this rank's shard."""
         a = self._codes([p[0] for p in pairs])
         b = self._codes([p[1] for p in pairs])
         lim = self.path_limit if limit is None else limit

@@ -156,7 +156,7 @@ def merge_hits(counts, hits_per_rank):
     total = int(off[-1])
     dtype = hits_per_rank[0].dtype
     hits = np.zeros(total, dtype=dtype)
-    owner = np.zeros(total, dtype=np.int32)
+    owner = np.zeros(total, dtype=np.int32)    # (returned as uint8: world <= 64)
     before = np.zeros(n_q, dtype=np.int64)          # hits of the same pair on lower ranks
     for r in range(world):
         c = counts[r]
@@ -168,7 +168,7 @@ def merge_hits(counts, hits_per_rank):
             hits[dest] = hits_per_rank[r][:n_r]
             owner[dest] = r
         before += c
-    return off.astype(np.uint64), hits, owner
+    return off.astype(np.uint64), hits, owner.astype(np.uint8)
 
 
 def merge_hits_torch(counts, recv, totals):
@@ -182,7 +182,7 @@ def merge_hits_torch(counts, recv, totals):
     torch.cumsum(counts.sum(dim=0), 0, out=off[1:])
     total = int(off[-1].item())
     hits = torch.zeros((total, 4), dtype=torch.int32, device=dev)
-    owner = torch.zeros(total, dtype=torch.int32, device=dev)
+    owner = torch.zeros(total, dtype=torch.uint8, device=dev)         # world <= 64 (csrc/comm.cu)
     before = torch.cumsum(counts, 0) - counts             # hits of the same pair on lower ranks
     pairs = torch.arange(n_q, device=dev)
     for r in range(world):
@@ -260,18 +260,21 @@ def exchange_hits_device(off_t, hits_t, type_base):
     if dev.type != "cuda":        # CPU tensors (the gloo tests): nothing to copy out
         return (goff.numpy().astype(np.uint64), ghits.contiguous().numpy().reshape(-1).view(HIT_DTYPE).copy(),
                 owner.numpy())
-    # one copy out, into pinned memory kept between calls
-    global _PINNED_HITS
+    # one copy out, into pinned memory kept between calls.  The returned arrays are VIEWS of it, valid until the next
+    # call (a private copy of 14 M hits = 227 MB cost more than the whole exchange).
+    global _PINNED_HITS, _PINNED_OWNER
     if _PINNED_HITS is None or _PINNED_HITS.shape[0] < n:
         _PINNED_HITS = torch.empty((max(int(n * 1.25), 1 << 16), 4), dtype=torch.int32, pin_memory=True)
+        _PINNED_OWNER = torch.empty(_PINNED_HITS.shape[0], dtype=torch.uint8, pin_memory=True)
     _PINNED_HITS[:n].copy_(ghits, non_blocking=True)
-    owner_h, goff_h = owner.cpu(), goff.cpu()
+    _PINNED_OWNER[:n].copy_(owner, non_blocking=True)
+    goff_h = goff.cpu()
     torch.cuda.synchronize(dev)
-    return (goff_h.numpy().astype(np.uint64), _PINNED_HITS[:n].numpy().reshape(-1).view(HIT_DTYPE).copy(),
-            owner_h.numpy())
+    return (goff_h.numpy().view(np.uint64), _PINNED_HITS[:n].numpy().reshape(-1).view(HIT_DTYPE), _PINNED_OWNER[:n].numpy())
 
 
 _PINNED_HITS = None
+_PINNED_OWNER = None
 
 
 def gather_objects(obj):
