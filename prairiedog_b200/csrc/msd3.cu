@@ -214,8 +214,9 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uin
         if (!full && tid < M3_TILE_WORDS) vm[tid] = m3_valid_word(ct, w0 + tid, info & ~M3_SIMPLE, kv);
         __syncthreads();
         const uint32_t pbase = (uint32_t)(w0 << 5) + w * M3_WARP_TILE + lane;
-        // only the digit stays in registers; the code is formed again from the staged words when the record is staged
         uint32_t dg[M3_ITEMS];
+#ifdef M3_P1_RECOMPUTE
+        // round 1: only the digit stays in registers, the code is formed again from the staged words at scatter time
         auto rec = [&](int j) { return make_uint2(pbase + 32 * j, m3_code_at(wrow[j], wrow[j + 1], lane, k)); };
         if (full) {
 #pragma unroll
@@ -227,6 +228,24 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB) m3_pass1_kernel(const uin
                 dg[j] = ((vm[w * M3_ITEMS + j] >> lane) & 1u) ? (m3_code_at(wrow[j], wrow[j + 1], lane, k) >> sh3) : B3;
             m3_partition_tile2<false, NBITS, false>(sm, rec, dg, (int)B3, dig, out, nullptr);
         }
+#else
+        // the 8 codes stay in registers (pass 1 holds no records, so there is room at 48 registers): forming them
+        // again at scatter time cost two broadcast LDS.64 per item, and ncu shows pass 1 stalled on shared-memory
+        // latency (short_scoreboard 3.5 per issue, profiles/r02_ncu_full_k11_summary.txt)
+        uint32_t code[M3_ITEMS];
+#pragma unroll
+        for (int j = 0; j < M3_ITEMS; ++j) code[j] = m3_code_at(wrow[j], wrow[j + 1], lane, k);
+        auto rec = [&](int j) { return make_uint2(pbase + 32 * j, code[j]); };
+        if (full) {
+#pragma unroll
+            for (int j = 0; j < M3_ITEMS; ++j) dg[j] = code[j] >> sh3;
+            m3_partition_tile2<false, NBITS, true>(sm, rec, dg, (int)B3, dig, out, nullptr);
+        } else {
+#pragma unroll
+            for (int j = 0; j < M3_ITEMS; ++j) dg[j] = ((vm[w * M3_ITEMS + j] >> lane) & 1u) ? (code[j] >> sh3) : B3;
+            m3_partition_tile2<false, NBITS, false>(sm, rec, dg, (int)B3, dig, out, nullptr);
+        }
+#endif
     }
 }
 

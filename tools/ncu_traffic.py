@@ -31,8 +31,9 @@ def main():
                 res[key] = (rd + wr) / u
                 detail[key] = {"dram_read_bytes": rd, "dram_write_bytes": wr, "units": u,
                                "gpu_time_us": r[col["gpu__time_duration.sum"]]}
-    json.dump({"source": rep, "how": "ncu --set full --clock-control none, one launch each, tools/profile_step.py 20 "
-               "(20 genomes, 1.0e8 k-mer records, 1.01e8 FASTA bytes)", "dram_bytes_per_unit": res, "launches": detail},
+    json.dump({"source": rep, "how": "ncu --set full --clock-control none, one launch each (the second, warm build of "
+               "tools/profile_step.py): %.4g k-mer records, %.4g FASTA bytes" % (n_rec, n_bytes),
+               "dram_bytes_per_unit": res, "launches": detail},
               open(out_path, "w"), indent=1)
     print(json.dumps(res, indent=1))
 

@@ -17,9 +17,9 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "tma": (256, 8, 5),                      # the product: next tile of passes 2-3 prefetched by cp.async.bulk
-    "notma": (256, 8, 5, "src:b914e62"),     # the same core, tiles loaded by the threads themselves
-    "r1core": (256, 8, 5, "src:fa473bf"),    # round 1's core (msd3.cu / msd3.cuh of that commit)
+    "p1regs": (256, 8, 5),                             # the product: pass 1 keeps its 8 codes in registers
+    "p1recompute": (256, 8, 5, "-DM3_P1_RECOMPUTE"),   # pass 1 forms the code again at scatter time (round 1)
+    "r1core": (256, 8, 5, "src:fa473bf"),              # round 1's core (msd3.cu / msd3.cuh of that commit)
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
 
