@@ -153,6 +153,7 @@ struct pdg_graph {
     const uint64_t *u_codes = nullptr;   // points at g_codes, x_codes or u_codes_buf
 
     // ---- scratch ----
+    pdg::DevBuf m3_d1;                    // msd3.cu: low byte of the code of every pass-2 output record (pass 3 counts from it)
     pdg::DevBuf m3_tile_info, m3_gbase;   // msd3.cu: per-tile contig info; per-group cell bases + record offsets
     struct M3Group { uint64_t pos0, pos1, rec_off; };
     pdg::DevBuf ml_flag;                 // msdlong.cu: window overflow flag

@@ -106,10 +106,13 @@ __device__ __forceinline__ void m3_clear_table2(M3Smem2 &sm) {
 // thread needs the tile's INPUT any more (the records are in registers); passes 2-3 start the copy of the next tile there
 struct M3NoHook { __device__ __forceinline__ void operator()() const {} };
 
+// out1 != nullptr: the low byte of every record's code is also written to out1[offset of the record] (pass 2: digit 1
+// of the record as one byte, so that pass 3 counts its bucket from 1 byte per record instead of re-reading 8)
 template <bool OUT4, int NBITS, bool FULL, typename RecFn, typename DigitFn, typename HookFn = M3NoHook>
 __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const uint32_t (&dg)[M3_ITEMS], const int BINS,
                                                    DigitFn digit, uint64_t *__restrict__ out8,
-                                                   uint32_t *__restrict__ out4, HookFn after_rank = HookFn()) {
+                                                   uint32_t *__restrict__ out4, HookFn after_rank = HookFn(),
+                                                   uint8_t *__restrict__ out1 = nullptr) {
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t pk[M3_ITEMS];      // slot in wcnt (low 16 bits) | rank inside the (warp, bin) run (high 16); ~0u = no record
@@ -189,6 +192,7 @@ __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const
             const uint2 x = sm.stage[s];
             const uint32_t at = sm.delta[digit(x.y)] + s;
             if (OUT4) out4[at] = x.x; else out8[at] = ((uint64_t)x.y << 32) | x.x;
+            if (!OUT4 && out1) out1[at] = (uint8_t)x.y;
         }
     }
     __syncthreads();
