@@ -154,6 +154,7 @@ struct pdg_graph {
 
     // ---- scratch ----
     pdg::DevBuf m3_d1;                    // msd3.cu: low byte of the code of every pass-2 output record (pass 3 counts from it)
+    bool m3_use_d1 = false;               // ... used by the staged groups since the last msd3_reserve (pipelined builds)
     pdg::DevBuf m3_tile_info, m3_gbase;   // msd3.cu: per-tile contig info; per-group cell bases + record offsets
     struct M3Group { uint64_t pos0, pos1, rec_off; };
     pdg::DevBuf ml_flag;                 // msdlong.cu: window overflow flag

@@ -361,38 +361,53 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB3) m3_pass3_kernel(const ui
     for (uint32_t gi = 0; gi < n_groups; ++gi) {
         const uint32_t *gb = gbase + (size_t)gi * cells1;
         const uint32_t sb = goff[gi] + gb[cell], se = goff[gi] + gb[cell + 1];
-        // Counted from pass 2's side array: ONE byte per record (the low byte of its code).  Counting from the records
-        // themselves read the bucket twice -- once here, once for the partition below -- and at config-3 scale the
-        // second read no longer hits L2 (592 buckets of 244 KB in flight > 126 MB): ncu measured 21.2 B of DRAM
-        // traffic per record against 12 algorithmic (profiles/traffic.json of round 2, before this change).
-        // Word-wise: thread t takes the aligned 32-bit words t, t + 256, ... of the segment; the first and the last
-        // word are masked by index.
-        const uint32_t w_first = sb >> 2, w_last = (se + 3) >> 2;          // words [w_first, w_last)
-        const uint32_t *d32 = reinterpret_cast<const uint32_t *>(in_d1);
-        uint32_t wd = w_first + tid;
-        // interior words in blocks of M3_COUNT_UNROLL loads in flight, no index tests
-        for (; wd + (M3_COUNT_UNROLL - 1) * M3_THREADS < w_last; wd += M3_COUNT_UNROLL * M3_THREADS) {
-            uint32_t v[M3_COUNT_UNROLL];
+        if (in_d1) {
+            // Counted from pass 2's side array: ONE byte per record (the low byte of its code).  Counting from the
+            // records reads the bucket twice -- once here, once for the partition below -- and at config-3 scale the
+            // second read no longer hits L2 (592 buckets of 244 KB in flight > 126 MB): ncu measured 21.2 B of DRAM
+            // traffic per record against 12 algorithmic.  The side array costs pass 2 5e8 scattered byte stores
+            // (2.14 -> 2.90 ms), so the host uses it only where pass 2 is hidden and pass 3 exposed: the pipelined
+            // build (profiles/r02_tune_d1byte.txt).
+            // Word-wise: thread t takes the aligned 32-bit words t, t + 256, ... of the segment; words at the two
+            // ends are masked by index.
+            const uint32_t w_first = sb >> 2, w_last = (se + 3) >> 2;          // words [w_first, w_last)
+            const uint32_t *d32 = reinterpret_cast<const uint32_t *>(in_d1);
+            uint32_t wd = w_first + tid;
+            for (; wd + (M3_COUNT_UNROLL - 1) * M3_THREADS < w_last; wd += M3_COUNT_UNROLL * M3_THREADS) {
+                uint32_t v[M3_COUNT_UNROLL];
 #pragma unroll
-            for (int u = 0; u < M3_COUNT_UNROLL; ++u) v[u] = d32[wd + u * M3_THREADS];
+                for (int u = 0; u < M3_COUNT_UNROLL; ++u) v[u] = d32[wd + u * M3_THREADS];
 #pragma unroll
-            for (int u = 0; u < M3_COUNT_UNROLL; ++u) {
-                const uint32_t i0 = (wd + u * M3_THREADS) << 2;
-                if (i0 >= sb && i0 + 3 < se) {
+                for (int u = 0; u < M3_COUNT_UNROLL; ++u) {
+                    const uint32_t i0 = (wd + u * M3_THREADS) << 2;
+                    if (i0 >= sb && i0 + 3 < se) {
 #pragma unroll
-                    for (int b = 0; b < 4; ++b) atomicAdd(&sm.delta[(v[u] >> (8 * b)) & m1], 1u);
-                } else {
+                        for (int b = 0; b < 4; ++b) atomicAdd(&sm.delta[(v[u] >> (8 * b)) & m1], 1u);
+                    } else {
 #pragma unroll
-                    for (int b = 0; b < 4; ++b)
-                        if (i0 + b >= sb && i0 + b < se) atomicAdd(&sm.delta[(v[u] >> (8 * b)) & m1], 1u);
+                        for (int b = 0; b < 4; ++b)
+                            if (i0 + b >= sb && i0 + b < se) atomicAdd(&sm.delta[(v[u] >> (8 * b)) & m1], 1u);
+                    }
                 }
             }
-        }
-        for (; wd < w_last; wd += M3_THREADS) {
-            const uint32_t v = d32[wd], i0 = wd << 2;
+            for (; wd < w_last; wd += M3_THREADS) {
+                const uint32_t v = d32[wd], i0 = wd << 2;
 #pragma unroll
-            for (int b = 0; b < 4; ++b)
-                if (i0 + b >= sb && i0 + b < se) atomicAdd(&sm.delta[(v >> (8 * b)) & m1], 1u);
+                for (int b = 0; b < 4; ++b)
+                    if (i0 + b >= sb && i0 + b < se) atomicAdd(&sm.delta[(v >> (8 * b)) & m1], 1u);
+            }
+        } else {
+            // from the records themselves: whole blocks of M3_COUNT_UNROLL x M3_THREADS records without a guard, the
+            // tail one record per thread and trip
+            uint32_t i = sb + tid;
+            for (; i + (M3_COUNT_UNROLL - 1) * M3_THREADS < se; i += M3_COUNT_UNROLL * M3_THREADS) {
+                uint32_t cd[M3_COUNT_UNROLL];
+#pragma unroll
+                for (int u = 0; u < M3_COUNT_UNROLL; ++u) cd[u] = in[i + u * M3_THREADS].y;
+#pragma unroll
+                for (int u = 0; u < M3_COUNT_UNROLL; ++u) atomicAdd(&sm.delta[cd[u] & m1], 1u);
+            }
+            for (; i < se; i += M3_THREADS) atomicAdd(&sm.delta[in[i].y & m1], 1u);
         }
     }
     __syncthreads();
@@ -551,7 +566,10 @@ void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_g
     // + 64: a bulk copy (tma.cuh) rounds its span to 16 bytes, i.e. reads up to one record past the last one
     g->recA.reserve(std::max<size_t>(n * 8, n_codes * 4) + 64, s);
     g->recB.reserve(std::max<size_t>(n * 8, 16) + 64, s);
-    g->m3_d1.reserve(n + 64, s);                                                                      // digit 1 of every record of recB
+    // digit 1 of every record of recB as one byte, for pass 3's count: only when the build is pipelined (several
+    // groups: pass 2 then runs under the host->device copies and pass 3 is the exposed tail; see m3_pass3_kernel)
+    g->m3_use_d1 = max_groups > 1;
+    if (g->m3_use_d1) g->m3_d1.reserve(n + 64, s);
     g->g_pos.reserve(std::max<size_t>(n * 4, 16), s);
     g->m3_tile_info.reserve((size_t)(pl.n_tiles + 1) * 4, s);
     g->m3_gbase.reserve((size_t)max_groups * (cells + 1) * 4 + (size_t)max_groups * 4, s);
@@ -617,7 +635,7 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
     mark(3);
     m3_pass2_kernel<7><<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem2), s>>>(g->recA.as<uint2>() + rec_off, pl, H1T, H12, base32,
                                                                           g->recB.as<uint64_t>() + rec_off,
-                                                                          g->m3_d1.as<uint8_t>() + rec_off);
+                                                                          g->m3_use_d1 ? g->m3_d1.as<uint8_t>() + rec_off : nullptr);
     PDG_LAUNCHED(g);
     mark(4);
     g->m3_timed = timed;
@@ -649,7 +667,8 @@ void msd3_finish_launch(pdg_graph *g, bool rows) {
         PDG_LAUNCHED(g);
     }
     m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem2), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
-                                                               g->g_pos.as<uint32_t>(), g->m3_d1.as<uint8_t>());
+                                                               g->g_pos.as<uint32_t>(),
+                                                               g->m3_use_d1 ? g->m3_d1.as<uint8_t>() : nullptr);
     PDG_LAUNCHED(g);
     if (G == 1 && g->m3_timed)   // the group's other stages were timed
         PDG_CUDA(cudaEventRecord(g->k_events[5], s));
