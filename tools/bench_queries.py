@@ -247,7 +247,11 @@ def main():
         if a.check:
             checked, compared = oracle_check(a, rng, qa, qb, ga, off, hits, orc, bufs, type_base, a.check)
         line.update({"metric": "batched_path_queries_per_sec", "value": Q / (ms * 1e-3), "unit": "queries/s",
-                     "n_gpus": world, "ms_per_batch": ms, "ms_per_batch_local_kernels": ms_local, "queries": Q,
+                     "n_gpus": world, "ms_per_batch": ms, "ms_per_batch_local_kernels": ms_local,
+                     "ms_per_batch_local_kernels_note": "this rank's shard only, through Engine.query_paths: kernels + the "
+                                                        "copy of its hits into a PAGEABLE host array (the collective form "
+                                                        "keeps them on the device and copies the merged answer out once, "
+                                                        "through pinned memory -- it can be the faster of the two)", "queries": Q,
                      "hits": int(hits.size), "positives": int(pos_idx.size), "positives_missing_own_hit": missing,
                      "oracle_checked": checked, "oracle_compared_hits": compared, "oracle_genomes": orc,
                      "k": a.k, "limit": a.limit, "genomes": a.genomes, "genomes_per_gpu": per,
