@@ -434,50 +434,58 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB3) m3_pass3_kernel(const ui
 #pragma unroll
         for (int i = 0; i < M3_BPT; ++i) {
             const int b = tid * M3_BPT + i;
-            if (b < M3_MAX_BINS) sm.cursor[b] = ex;
             if (b < (int)B1) rowtab[((size_t)cell << pl.b1) + b] = ex;
             ex += v[i];
+            if (b < M3_MAX_BINS) sm.cursor[b] = ex;     // the END of the row: the tiles are walked backwards (below)
         }
     }
     __syncthreads();
     const uint32_t li0 = w * M3_WARP_TILE + lane;
     auto dig = [m1](uint32_t cd) { return cd & m1; };
-    // The tiles of the bucket, segment after segment, fetched one ahead by bulk asynchronous copies (see pass 2).
-    // (gi, t0, se) = the current tile's group, first record and the end of its segment; every thread walks the same
-    // sequence, thread 0 issues the copies.
+    // The tiles of the bucket are walked BACKWARDS -- last segment first, inside a segment from its end -- with cursors
+    // that start at the end of every row and move down.  The count sweep above read the bucket front to back; walking
+    // it front to back again is the worst case for the L2: 592 buckets of 244 KB are in flight against 126 MB, so
+    // by the time the second sweep starts the front of the bucket is the oldest data and gone (ncu: 21.2 B of DRAM
+    // traffic per record against 12 algorithmic).  Backwards, the second sweep starts on what was read last.
+    // Tiles are fetched one ahead by bulk asynchronous copies (see pass 2); every thread walks the same sequence,
+    // thread 0 issues the copies.  (gi, sb, hi) = group of the current tile, start of its segment, end of the tile.
     auto segment = [&](uint32_t g, uint32_t &b0, uint32_t &e0) {
         const uint32_t *gb = gbase + (size_t)g * cells1;
         b0 = goff[g] + gb[cell];
         e0 = goff[g] + gb[cell + 1];
     };
-    // first tile at or after (g, t) -- skips empty segments; false when the bucket is exhausted
-    auto settle = [&](uint32_t &g, uint32_t &t, uint32_t &e) {
-        while (g < n_groups) {
-            if (t < e) return true;
-            if (++g < n_groups) segment(g, t, e);
+    // the tile that ends at or before (g, h) -- skips empty segments; false when the bucket is exhausted
+    auto settle = [&](int &g, uint32_t &b0, uint32_t &h) {
+        while (g >= 0) {
+            if (h > b0) return true;
+            if (--g >= 0) segment((uint32_t)g, b0, h);
         }
         return false;
     };
-    uint32_t gi = 0, t0 = 0, se = 0;
-    if (n_groups) segment(0, t0, se);
-    bool have = settle(gi, t0, se);
+    int gi = (int)n_groups - 1;
+    uint32_t sb = 0, hi = 0;
+    if (gi >= 0) segment((uint32_t)gi, sb, hi);
+    bool have = settle(gi, sb, hi);
     if (tid == 0) {
         tma_bar_init(&bar, 1);
         if (have) {
-            const TmaSpan sp = tma_span8(in + t0, min((uint32_t)M3_TILE, se - t0));
+            const uint32_t n0 = min((uint32_t)M3_TILE, hi - sb);
+            const TmaSpan sp = tma_span8(in + (hi - n0), n0);
             tma_load(inbuf, sp.src, sp.bytes, &bar);
         }
     }
     __syncthreads();
     uint32_t parity = 0;
     while (have) {
-        const uint32_t tile_n = min((uint32_t)M3_TILE, se - t0);
+        const uint32_t tile_n = min((uint32_t)M3_TILE, hi - sb), t0 = hi - tile_n;
         const uint2 *src = inbuf + tma_span8(in + t0, tile_n).skip + li0;
-        uint32_t ngi = gi, nt0 = t0 + M3_TILE, nse = se;
-        const bool nhave = settle(ngi, nt0, nse);
+        int ngi = gi;
+        uint32_t nsb = sb, nhi = t0;
+        const bool nhave = settle(ngi, nsb, nhi);
         auto prefetch = [&]() {
             if (tid == 0 && nhave) {
-                const TmaSpan sp = tma_span8(in + nt0, min((uint32_t)M3_TILE, nse - nt0));
+                const uint32_t n1 = min((uint32_t)M3_TILE, nhi - nsb);
+                const TmaSpan sp = tma_span8(in + (nhi - n1), n1);
                 tma_load(inbuf, sp.src, sp.bytes, &bar);
             }
         };
@@ -491,7 +499,8 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB3) m3_pass3_kernel(const ui
 #pragma unroll
             for (int j = 0; j < M3_ITEMS; ++j) dg[j] = r[j].y & m1;
             auto rec = [&](int j) { return r[j]; };
-            m3_partition_tile2<true, NBITS, true>(sm, rec, dg, (int)B1, dig, nullptr, out_pos, prefetch);
+            m3_partition_tile2<true, NBITS, true, decltype(rec), decltype(dig), decltype(prefetch), true>(
+                sm, rec, dg, (int)B1, dig, nullptr, out_pos, prefetch);
         } else {
 #pragma unroll
             for (int j = 0; j < M3_ITEMS; ++j) {
@@ -500,9 +509,10 @@ __global__ void __launch_bounds__(M3_THREADS, M3_MINB3) m3_pass3_kernel(const ui
                 dg[j] = ok ? (r[j].y & m1) : B1;
             }
             auto rec = [&](int j) { return r[j]; };
-            m3_partition_tile2<true, NBITS, false>(sm, rec, dg, (int)B1, dig, nullptr, out_pos, prefetch);
+            m3_partition_tile2<true, NBITS, false, decltype(rec), decltype(dig), decltype(prefetch), true>(
+                sm, rec, dg, (int)B1, dig, nullptr, out_pos, prefetch);
         }
-        gi = ngi; t0 = nt0; se = nse; have = nhave;
+        gi = ngi; sb = nsb; hi = nhi; have = nhave;
     }
 }
 

@@ -108,7 +108,10 @@ struct M3NoHook { __device__ __forceinline__ void operator()() const {} };
 
 // out1 != nullptr: the low byte of every record's code is also written to out1[offset of the record] (pass 2: digit 1
 // of the record as one byte, so that pass 3 counts its bucket from 1 byte per record instead of re-reading 8)
-template <bool OUT4, int NBITS, bool FULL, typename RecFn, typename DigitFn, typename HookFn = M3NoHook>
+// REV: the tiles of a range are walked from the LAST to the first: on entry sm.cursor[b] is the global offset just PAST
+// bin b's records of this tile and on exit it has moved down by the tile's count (pass 3, see there).  The order inside
+// a tile is unchanged, so the partition stays stable.
+template <bool OUT4, int NBITS, bool FULL, typename RecFn, typename DigitFn, typename HookFn = M3NoHook, bool REV = false>
 __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const uint32_t (&dg)[M3_ITEMS], const int BINS,
                                                    DigitFn digit, uint64_t *__restrict__ out8,
                                                    uint32_t *__restrict__ out4, HookFn after_rank = HookFn(),
@@ -168,9 +171,9 @@ __device__ __forceinline__ void m3_partition_tile2(M3Smem2 &sm, RecFn rec, const
         if (!FULL) all = sum;
         if (tid < BINS) {
             uint32_t run = base + inc - tot;            // start of bin tid inside the tile
-            const uint32_t cur = sm.cursor[tid];
+            const uint32_t cur = REV ? sm.cursor[tid] - tot : sm.cursor[tid];
             sm.delta[tid] = cur - run;
-            sm.cursor[tid] = cur + tot;
+            sm.cursor[tid] = REV ? cur : cur + tot;
 #pragma unroll
             for (int ww = 0; ww < M3_WARPS; ++ww) {
                 const uint32_t cw = sm.wcnt[ww * M3_MAX_BINS + tid];

@@ -17,8 +17,8 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "d1byte": (256, 8, 5),                             # the product: pass 3 counts from pass 2's one-byte-per-record side array
-    "d1rec": (256, 8, 5, "src:8ab3606"),               # pass 3 counts from the 8-byte records (reads its bucket twice)
+    "p3rev": (256, 8, 5),                              # the product: pass 3 walks its bucket backwards after the count sweep
+    "p3fwd": (256, 8, 5, "src:d60f7ad"),               # both sweeps front to back
     "r1core": (256, 8, 5, "src:fa473bf"),              # round 1's core (msd3.cu / msd3.cuh of that commit)
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
