@@ -541,8 +541,8 @@ __global__ void m3_compact_rows_kernel(const uint32_t *__restrict__ rowtab, cons
 //   msd3_finish       pass 3 over the cells (segments of all groups in order) + rows
 static M3Plan m3_plan(int k, uint64_t pos0, uint64_t pos1) {
     M3Plan pl{};
-    pl.b1 = std::min(8, 2 * k);
-    pl.b2 = std::min(7, 2 * k - pl.b1);
+    pl.b1 = std::min(M3_B1, 2 * k);
+    pl.b2 = std::min(M3_B2, 2 * k - pl.b1);
     pl.b3 = 2 * k - pl.b1 - pl.b2;
     pl.base0 = pos0 & ~31ULL;
     pl.n_tiles = (uint32_t)((pos1 - pl.base0 + M3_TILE - 1) / M3_TILE);
@@ -588,10 +588,10 @@ void msd3_reserve(pdg_graph *g, uint64_t pos_lo, uint64_t pos_hi, uint32_t max_g
     g->m3_max_groups = max_groups;
     g->m3_pos_lo = pos_lo;
     if (!(g->attr_mask & pdg_graph::ATTR_MSD3)) {
-        PDG_CUDA(cudaFuncSetAttribute(m3_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 1 << 16));
+        PDG_CUDA(cudaFuncSetAttribute(m3_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << (22 - M3_B1)));
         PDG_CUDA(cudaFuncSetAttribute(m3_pass1_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem2)));
-        PDG_CUDA(cudaFuncSetAttribute(m3_pass2_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem2)));
-        PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem2)));
+        PDG_CUDA(cudaFuncSetAttribute(m3_pass2_kernel<M3_B2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem2)));
+        PDG_CUDA(cudaFuncSetAttribute(m3_pass3_kernel<M3_B1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(M3Smem2)));
         g->attr_mask |= pdg_graph::ATTR_MSD3;
     }
 }
@@ -643,7 +643,7 @@ void msd3_stage_group(pdg_graph *g, const ContigTable &ct, uint64_t pos0, uint64
                                                                      g->recA.as<uint64_t>() + rec_off);
     PDG_LAUNCHED(g);
     mark(3);
-    m3_pass2_kernel<7><<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem2), s>>>(g->recA.as<uint2>() + rec_off, pl, H1T, H12, base32,
+    m3_pass2_kernel<M3_B2><<<pl.n_chunks * B3, M3_THREADS, sizeof(M3Smem2), s>>>(g->recA.as<uint2>() + rec_off, pl, H1T, H12, base32,
                                                                           g->recB.as<uint64_t>() + rec_off,
                                                                           g->m3_use_d1 ? g->m3_d1.as<uint8_t>() + rec_off : nullptr);
     PDG_LAUNCHED(g);
@@ -676,7 +676,7 @@ void msd3_finish_launch(pdg_graph *g, bool rows) {
         m3_base_kernel<<<1, 1024, 0, s>>>(tot32, cells, base32, nullptr, 0u);
         PDG_LAUNCHED(g);
     }
-    m3_pass3_kernel<8><<<cells, M3_THREADS, sizeof(M3Smem2), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
+    m3_pass3_kernel<M3_B1><<<cells, M3_THREADS, sizeof(M3Smem2), s>>>(g->recB.as<uint2>(), pl, gbase, goff, G, base32, rowtab,
                                                                g->g_pos.as<uint32_t>(),
                                                                g->m3_use_d1 ? g->m3_d1.as<uint8_t>() : nullptr);
     PDG_LAUNCHED(g);

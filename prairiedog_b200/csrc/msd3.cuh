@@ -18,6 +18,15 @@ static constexpr int M3_MINB = M3_CFG_MINB;                       // CTAs per SM
 #define M3_CFG_MINB3 4   /* pass 3 is the one pass that spills at 48 registers: 4 CTAs/SM (64 registers) 2.69 ms, 5: 2.81 ms */
 #endif
 static constexpr int M3_MINB3 = M3_CFG_MINB3;
+// widths of the low and the middle digit at k = 11 (the high digit takes the rest, <= 7 bits).  8|7: buckets of pass 3
+// of ~30 K records at config 3; 7|8: ~15 K records that stay in L2 between pass 3's two sweeps -- measured: pass 3
+// 2.64 -> 2.43 ms, pass 2 2.14 -> 2.83 ms (64-byte runs per bin and tile), profiles/r02_tune_split78.txt.  8|7 it is.
+#ifndef M3_CFG_B1
+#define M3_CFG_B1 8
+#define M3_CFG_B2 7
+#endif
+static constexpr int M3_B1 = M3_CFG_B1, M3_B2 = M3_CFG_B2;
+static_assert(M3_B1 <= 8 && M3_B2 <= 8 && M3_B1 + M3_B2 == 15, "digit split");
 static constexpr int M3_TILE = M3_THREADS * M3_ITEMS;   // items per tile
 static constexpr int M3_WARP_TILE = 32 * M3_ITEMS;      // consecutive items per warp
 static constexpr int M3_MAX_BINS = 256;

@@ -17,9 +17,9 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "p3rev": (256, 8, 5),                              # the product: pass 3 walks its bucket backwards after the count sweep
-    "p3fwd": (256, 8, 5, "src:d60f7ad"),               # both sweeps front to back
-    "r1core": (256, 8, 5, "src:fa473bf"),              # round 1's core (msd3.cu / msd3.cuh of that commit)
+    "split87": (256, 8, 5),                                            # the product: digits 7|7|8 (high to low) at k = 11
+    "split78": (256, 8, 5, "-DM3_CFG_B1=7", "-DM3_CFG_B2=8"),          # 7|8|7: pass-3 buckets of ~15 K records
+    "split78m5": (256, 8, 5, "-DM3_CFG_B1=7", "-DM3_CFG_B2=8", "-DM3_CFG_MINB3=5"),
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
 
