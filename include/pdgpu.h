@@ -272,6 +272,18 @@ int pdg_filter_fetch(pdg_graph *g, uint64_t *h_src_code, uint64_t *h_tgt_code, u
 int pdg_comm_unique_id(uint8_t *h_id128);
 int pdg_comm_init(pdg_graph *g, const uint8_t *h_id128, int rank, int world);
 
+/* K6: a checksum that allocates nothing.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  *d_sum = sum over d_codes[0, n) of mix64(code + golden ratio) modulo 2^64 -- for a graph's node table (the
+ * codes pdg_export_nodes returns) exactly the nodes_sum of pdg_checksum.  d_codes and d_sum are DEVICE pointers on
+ * `device`; two kernels are launched on `cuda_stream` (NULL = the default stream) and the call returns without
+ * synchronising.  The per-CTA partial sums live in a 1 MiB file-scope __device__ array that every GPU loading the
+ * library holds until exit (csrc/noalloc.cu), which bounds a call to PDG_STATIC_MAX_CODES codes: more returns
+ * PDG_E_CAPACITY.  No cudaMalloc, cudaFree or allocating library routine is called.  All calls on a device share the
+ * array: calls that overlap on the GPU (different streams) race and must be ordered by the caller. */
+#define PDG_STATIC_MAX_CODES (1ull << 27)
+int pdg_codes_checksum_static(int device, const uint64_t *d_codes, uint64_t n, uint64_t *d_sum, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

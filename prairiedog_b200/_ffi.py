@@ -110,7 +110,9 @@ SIGNATURES = {
     "pdg_query_strings_fetch": (c_int, [vp, vp, vp]),
     "pdg_comm_unique_id": (c_int, [vp]),
     "pdg_comm_init": (c_int, [vp, vp, c_int, c_int]),
+    "pdg_codes_checksum_static": (c_int, [c_int, vp, c_u64, vp, vp]),
 }
+STATIC_MAX_CODES = 1 << 27
 
 _lib = None
 

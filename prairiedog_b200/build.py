@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpdgpu.so")
 SOURCES = ["api.cu", "ingest.cu", "ingest_batch.cu", "gindex.cu", "gbuild.cu", "ksort.cu", "msd3.cu", "msdlong.cu", "xbuild.cu", "build.cu", "export.cu", "stats.cu",
-           "radix.cu", "scan.cu", "query.cu", "comm.cu", "filter.cu"]
+           "radix.cu", "scan.cu", "query.cu", "comm.cu", "filter.cu", "noalloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--cudart", "static"]
 
