@@ -18,6 +18,12 @@
 namespace pdg {
 
 static constexpr int ML_THREADS = 256;
+#ifndef ML_CFG_MINB
+#define ML_CFG_MINB 4   /* CTAs per SM the bucket sort is compiled for (64 registers) */
+#endif
+#ifndef ML_CFG_LB
+#define ML_CFG_LB 0     /* registers per batch of packed-word loads; 0 = one register at a time (faster: 16.4 vs 18.7 ms) */
+#endif
 
 __device__ __forceinline__ unsigned long long ml_code_at(const unsigned long long *__restrict__ packed, uint32_t p, int k) {
     const uint32_t w = p >> 5, off = p & 31u;
@@ -149,12 +155,58 @@ __device__ __forceinline__ void ml_sort_bucket(const unsigned long long *__restr
     const int sb = 2 * k - kMsd3MaxBits;                       // suffix bits, <= 40
     const unsigned long long smask = (1ULL << sb) - 1ULL;
     unsigned long long key[E];
+#if ML_CFG_LB == 0
+    // register by register: position, then its packed words.  The compiler keeps that order (2 E dependent trips to
+    // memory per bucket, all of them long_scoreboard stalls in ncu's source page) -- and it is the FASTER form: see
+    // the batched one below.
 #pragma unroll
     for (int r = 0; r < E; ++r) {
         const uint32_t i = r * 32 + lane;
+#ifdef ML_FAKE_GATHER   /* experiment: no access to the packed store at all, keys from a hash of the position */
+        key[r] = i < m ? (((mix64(__ldcs(pos_in + e0 + i)) & smask) << 9) | i) : ~0ULL;
+#else
         key[r] = i < m ? (((ml_code_at(packed, __ldcs(pos_in + e0 + i), k) & smask) << 9) | i) : ~0ULL;
+#endif
     }
+#else
+    // Loads in batches, every batch's loads independent of each other: first the positions of all E registers, then
+    // -- ML_LB registers at a time -- both packed words of every position, then the keys.  Measured SLOWER at config 3
+    // (18.4-19.4 ms for batches of 2, 4, 8 against 16.4 ms): more gathers in flight do not help a kernel whose
+    // gathers already run at what the DRAM gives for random 64-byte lines (profiles/r02_k31_bucket_sort_experiments.txt).
+    constexpr int ML_LB = E < ML_CFG_LB ? E : ML_CFG_LB;
+    {
+        uint32_t p[E];
+#pragma unroll
+        for (int r = 0; r < E; ++r) {
+            const uint32_t i = r * 32 + lane;
+            p[r] = i < m ? pos_in[e0 + i] : 0u;                // position 0: a harmless, hot line for the padding lanes
+        }
+#pragma unroll
+        for (int r0 = 0; r0 < E; r0 += ML_LB) {
+            unsigned long long w0[ML_LB], w1[ML_LB];
+#pragma unroll
+            for (int q = 0; q < ML_LB; ++q) {
+                const unsigned long long *src = packed + (p[r0 + q] >> 5);
+                w0[q] = src[0];
+                w1[q] = src[1];                                // the store has a word of slack behind the last residue
+            }
+#pragma unroll
+            for (int q = 0; q < ML_LB; ++q) {
+                const uint32_t i = (r0 + q) * 32 + lane, off = p[r0 + q] & 31u;
+                // window of 32 residues at `off` of the 64 in (w0, w1); a shift by 64 is split in two
+                const unsigned long long hi = (w0[q] << (2 * off)) | ((w1[q] >> 1) >> (63 - 2 * off));
+                key[r0 + q] = i < m ? ((((hi >> (64 - 2 * k)) & smask) << 9) | i) : ~0ULL;
+            }
+        }
+    }
+#endif
+#ifndef ML_NO_SORT      /* experiment: everything but the network (output unsorted) */
     ml_warp_bitonic<E>(key, lane);
+#endif
+    // the positions of the sorted records, all loads first (the bucket's slice of pos_in was read a moment ago)
+    uint32_t pv[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) pv[r] = (uint32_t)(r * 32 + lane) < m ? pos_in[e0 + (uint32_t)(key[r] & 511u)] : 0u;
     // a record starts a row when its code differs from its predecessor's (the first of a bucket always does)
     unsigned long long carry = ~0ULL;                          // suffix of key index r * 32 - 1
 #pragma unroll
@@ -166,7 +218,7 @@ __device__ __forceinline__ void ml_sort_bucket(const unsigned long long *__restr
         carry = __shfl_sync(0xffffffffu, sfx, 31);
         if (i < m) {
             const unsigned long long c = (prefix << sb) | sfx;
-            __stcs(out + e0 + i, make_uint4((uint32_t)c, (uint32_t)(c >> 32), pos_in[e0 + (uint32_t)(key[r] & 511u)], 0u));
+            __stcs(out + e0 + i, make_uint4((uint32_t)c, (uint32_t)(c >> 32), pv[r], 0u));
             __stcs(heads + e0 + i, (i == 0 || sfx != prev) ? 1u : 0u);
         }
     }
@@ -177,7 +229,8 @@ __device__ __forceinline__ void ml_sort_bucket(const unsigned long long *__restr
 // (Earlier versions, config-3 scale: windows of ~8 whole buckets sorted per CTA in shared memory, 40 ms --
 // the network is log^2 in the window size and half of every window was padding; one warp per bucket in
 // shared memory, 31.5 ms at 36 % issue -- every stage waits for a shared-memory round trip.)
-__global__ void __launch_bounds__(ML_THREADS, 4) ml_bucket_sort_kernel(const unsigned long long *__restrict__ packed,
+template <bool PIPE>
+__global__ void __launch_bounds__(ML_THREADS, ML_CFG_MINB) ml_bucket_sort_kernel(const unsigned long long *__restrict__ packed,
                                                                     const uint32_t *__restrict__ pos_in,
                                                                     const uint32_t *__restrict__ rowtab, uint32_t n_buckets,
                                                                     int k, uint4 *__restrict__ out,
@@ -186,9 +239,8 @@ __global__ void __launch_bounds__(ML_THREADS, 4) ml_bucket_sort_kernel(const uns
                                                                     uint32_t big_cap) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t nw = gridDim.x * (ML_THREADS / 32);
-    for (uint32_t b = blockIdx.x * (ML_THREADS / 32) + w; b < n_buckets; b += nw) {
-        const uint32_t e0 = rowtab[b], m = rowtab[b + 1] - e0;
-        if (m == 0) continue;
+    auto sort_one = [&](uint32_t b, uint32_t e0, uint32_t m) {
+        if (m == 0) return;
         if (m <= 32) ml_sort_bucket<1>(packed, pos_in, e0, m, k, b, lane, out, heads);
         else if (m <= 64) ml_sort_bucket<2>(packed, pos_in, e0, m, k, b, lane, out, heads);
         else if (m <= 128) ml_sort_bucket<4>(packed, pos_in, e0, m, k, b, lane, out, heads);
@@ -198,6 +250,46 @@ __global__ void __launch_bounds__(ML_THREADS, 4) ml_bucket_sort_kernel(const uns
             const unsigned int slot = atomicAdd(&ctl[1], 1u);
             if (slot < big_cap) big[slot] = make_uint2(e0, e0 + m); else atomicOr(&ctl[0], 1u);
         }
+    };
+    const uint32_t b0 = blockIdx.x * (ML_THREADS / 32) + w;
+    if (!PIPE) {
+        for (uint32_t b = b0; b < n_buckets; b += nw) {
+            const uint32_t e0 = rowtab[b];
+            sort_one(b, e0, rowtab[b + 1] - e0);
+        }
+        return;
+    }
+    // A warp's bucket costs three dependent trips to memory -- its bounds, its positions, the packed words its
+    // positions point at (a random 64-byte line each) -- before the first compare; with 8 warps per scheduler that
+    // chain showed as long_scoreboard, the top stall (ncu: issue slots 53 % used).  So the warp works three buckets
+    // ahead of itself: while bucket i is sorted, the lines of bucket i + 1 are on their way to L2 (prefetch from the
+    // positions loaded one iteration earlier), the first ML_PF x 32 positions of bucket i + 2 are being loaded and so
+    // are the bounds of bucket i + 3.
+    constexpr int ML_PF = 4;
+    auto bounds = [&](uint32_t b, uint32_t &e, uint32_t &m) {
+        e = 0; m = 0;
+        if (b < n_buckets) { e = rowtab[b]; m = rowtab[b + 1] - e; }
+    };
+    auto fetch_pos = [&](uint32_t e, uint32_t m, uint32_t (&P)[ML_PF]) {
+#pragma unroll
+        for (int q = 0; q < ML_PF; ++q) P[q] = (uint32_t)(q * 32 + lane) < m ? pos_in[e + q * 32 + lane] : ~0u;
+    };
+    uint32_t e_c, m_c, e_1, m_1, e_2, m_2, P[ML_PF];
+    bounds(b0, e_c, m_c);
+    bounds(b0 + nw, e_1, m_1);
+    bounds(b0 + 2 * nw, e_2, m_2);
+    fetch_pos(e_1, m_1, P);
+    for (uint32_t b = b0; b < n_buckets; b += nw) {
+#pragma unroll
+        for (int q = 0; q < ML_PF; ++q)
+            if (P[q] != ~0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(packed + (P[q] >> 5)));
+        fetch_pos(e_2, m_2, P);
+        uint32_t e_3, m_3;
+        bounds(b + 3 * nw, e_3, m_3);
+        sort_one(b, e_c, m_c);
+        e_c = e_1; m_c = m_1;
+        e_1 = e_2; m_1 = m_2;
+        e_2 = e_3; m_2 = m_3;
     }
 }
 
@@ -280,7 +372,10 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     // (an L2 persistence window over the packed store was tried for the random code gathers: the kernel
     // did not get faster and the rest of the step lost 16 ms to the limit / reset calls)
     PDG_CUDA(cudaEventRecord(g->k_events[6], s));
-    ml_bucket_sort_kernel<<<grid, ML_THREADS, 0, s>>>(packed, pos_in, rowtab, n_buckets, k, out, heads, ctl, big, big_cap);
+    // the three-buckets-ahead loop is measured SLOWER (20.8 against 16.4 ms at config 3): off unless asked for, kept for the A/B
+    static const bool pipe = getenv("PDG_ML_PIPE") && atoi(getenv("PDG_ML_PIPE")) != 0;
+    if (pipe) ml_bucket_sort_kernel<true><<<grid, ML_THREADS, 0, s>>>(packed, pos_in, rowtab, n_buckets, k, out, heads, ctl, big, big_cap);
+    else ml_bucket_sort_kernel<false><<<grid, ML_THREADS, 0, s>>>(packed, pos_in, rowtab, n_buckets, k, out, heads, ctl, big, big_cap);
     PDG_LAUNCHED(g);
     unsigned int h_ctl[4] = {0, 0, 0, 0};
     PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 8, cudaMemcpyDeviceToHost, s));

@@ -17,9 +17,10 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "split87": (256, 8, 5),                                            # the product: digits 7|7|8 (high to low) at k = 11
-    "split78": (256, 8, 5, "-DM3_CFG_B1=7", "-DM3_CFG_B2=8"),          # 7|8|7: pass-3 buckets of ~15 K records
-    "split78m5": (256, 8, 5, "-DM3_CFG_B1=7", "-DM3_CFG_B2=8", "-DM3_CFG_MINB3=5"),
+    "mlbase": (256, 8, 5),                               # k > 16 bucket sort as shipped
+    "mlfake": (256, 8, 5, "-DML_FAKE_GATHER"),           # experiment: keys from a hash of the position, no gather (wrong output)
+    "mlnosort": (256, 8, 5, "-DML_NO_SORT"),             # experiment: gather and write, no sorting network (wrong output)
+    "mlfakenosort": (256, 8, 5, "-DML_FAKE_GATHER", "-DML_NO_SORT"),   # streaming part only
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
 
