@@ -526,8 +526,10 @@ def kernel_table(st, k, peak):
         add("m3_hist_kernel (joint digit histograms from the packed genome)", st["ms_hist"], n, 0.25)
     if k > 16 and st["sort_passes"] == 4 and st["ms_sort_kernel_avg"] > 0:
         # (also when the prefix passes ran inside a pipelined ingest and have no event times of their own)
-        # reads a position, gathers the two packed words of its code, writes a 16-byte record + a row-head flag
-        add("ml_bucket_sort_kernel (prefix buckets -> records sorted on the full code)", st["ms_sort_kernel_avg"], n, 40.0)
+        # reads a position, gathers the two packed words of its code, writes the position, the 8-byte code and one
+        # row-head bit; the launches of all bucket-size classes (+ the CTA kernels of the few big buckets) timed together
+        add("ml_class_sort_kernel (prefix buckets -> position column, codes, row-head bits; all size classes)",
+            st["ms_sort_kernel_avg"], n, 32.125)
     elif st["ms_pass"][0] <= 0 and st["ms_sort_kernel_avg"] > 0:
         add("onesweep_kernel (one LSD partition pass)", st["ms_sort_kernel_avg"], n, 16.0 if k <= 16 else 32.0)
     add("fb_summ_kernel (FASTA bytes -> tile summaries)", st["ms_ingest_a"], nb, 1.0)

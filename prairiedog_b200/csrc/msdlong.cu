@@ -5,9 +5,10 @@
 // groups the positions into 4^11 buckets in three passes over 8-byte records.  A bucket holds
 // ~n / 4^11 positions (120 at config-3 scale) in ascending order; what is left is a stable sort of
 // every bucket on the remaining 2k - 22 bits: a warp reads the full code of each of the bucket's
-// records from the packed store, sorts the bucket on (code, position) in shared memory and writes
-// sorted {code, position} records, from which gbuild.cu forms the rows as before.  Buckets of more
-// than 512 records get a whole CTA (up to 16 384 records).
+// records from the packed store, sorts the bucket on (code, position) in registers and writes the
+// final position column, the code of every record and one bit per record that says "a row starts
+// here"; gbuild.cu forms the rows from the bits (rows_from_head_bits).  Buckets of more than 512
+// records get a whole CTA (up to 16 384 records).
 // The LSD path this replaces (radix.cu: 8 passes over 16-byte records, 256 B/record of traffic)
 // stays as the fallback for inputs whose buckets do not fit a window (long low-complexity repeats).
 // Reference counterpart: the node_idx / srcnode_idx / tgtnode_idx B-trees of lemongraph.c:591-630.
@@ -18,12 +19,32 @@
 namespace pdg {
 
 static constexpr int ML_THREADS = 256;
-#ifndef ML_CFG_MINB
-#define ML_CFG_MINB 4   /* CTAs per SM the bucket sort is compiled for (64 registers) */
+#ifndef ML_CFG_CLASSES
+#define ML_CFG_CLASSES 3   /* launches of the bucket sort by bucket-size class (see ml_class_sort_kernel); 1, 2 or 3 */
 #endif
-#ifndef ML_CFG_LB
-#define ML_CFG_LB 0     /* registers per batch of packed-word loads; 0 = one register at a time (faster: 16.4 vs 18.7 ms) */
+#ifndef ML_CFG_MINB_A
+#define ML_CFG_MINB_A 8    /* CTAs per SM of the class of buckets <= 128 records */
 #endif
+
+// What a bucket sort writes for record i of the sorted order (i = bucket start + rank inside the bucket, which IS the
+// record's final index: the buckets are in prefix order): its position, its full code, and bit i of `bits` when a row
+// (a new code) starts at i.  bits is zeroed before the launches; buckets do not end on word boundaries, so the bits go
+// in with atomicOr.  (Until round 2 the kernels wrote 16-byte {code, position} records plus one 32-bit flag per
+// record, and gbuild.cu made the rows with a scan over the 5e8 flags and a pass over the 8 GB of records: 5.5 ms of a
+// 27 ms step at config 3, profiles/r02_launches_k31_classes.csv.)
+struct MlOut {
+    uint32_t *pos;
+    unsigned long long *code;
+    unsigned int *bits;
+};
+
+// head bits of the 32 records that start at index g0 (bit l = record g0 + l); called by one lane
+__device__ __forceinline__ void ml_put_bits(unsigned int *__restrict__ bits, uint32_t g0, uint32_t mask) {
+    if (!mask) return;
+    const uint32_t sh = g0 & 31u;
+    atomicOr(&bits[g0 >> 5], mask << sh);
+    if (sh && (mask >> (32u - sh))) atomicOr(&bits[(g0 >> 5) + 1], mask >> (32u - sh));
+}
 
 __device__ __forceinline__ unsigned long long ml_code_at(const unsigned long long *__restrict__ packed, uint32_t p, int k) {
     const uint32_t w = p >> 5, off = p & 31u;
@@ -44,12 +65,11 @@ __device__ __forceinline__ uint32_t ml_first_bucket(const uint32_t *__restrict__
 }
 
 // Sorts records [e0, e0 + cnt) of pos_in on (code, position) in shared memory (key / val hold at least the
-// next power of two >= cnt entries) and writes them to out.  All threads of the CTA take part.
+// next power of two >= cnt entries) and writes them.  All threads of the CTA take part.
 template <int THREADS>
 __device__ __forceinline__ void ml_sort_range(const unsigned long long *__restrict__ packed,
                                               const uint32_t *__restrict__ pos_in, uint32_t e0, uint32_t cnt, int k,
-                                              unsigned long long *key, uint32_t *val, uint4 *__restrict__ out,
-                                              uint32_t *__restrict__ heads) {
+                                              unsigned long long *key, uint32_t *val, const MlOut &out) {
     const int tid = threadIdx.x;
     uint32_t tn = 2;           // sort the next power of two >= cnt
     while (tn < cnt) tn <<= 1;
@@ -81,215 +101,163 @@ __device__ __forceinline__ void ml_sort_range(const unsigned long long *__restri
         }
     }
     __syncthreads();
-    for (uint32_t i = tid; i < cnt; i += THREADS) {
-        const unsigned long long c = key[i];
-        out[e0 + i] = make_uint4((uint32_t)c, (uint32_t)(c >> 32), val[i], 0u);
-        heads[e0 + i] = (i == 0 || c != key[i - 1]) ? 1u : 0u;     // a bucket is a whole number of rows
+    for (uint32_t i0 = 0; i0 < cnt; i0 += THREADS) {     // whole warps: the ballot needs every lane
+        const uint32_t i = i0 + tid;
+        const bool ok = i < cnt;
+        const unsigned long long c = ok ? key[i] : 0ULL;
+        const bool head = ok && (i == 0 || c != key[i - 1]);     // a bucket is a whole number of rows
+        const uint32_t hm = __ballot_sync(0xffffffffu, head);
+        if (ok) {
+            out.pos[e0 + i] = val[i];
+            out.code[e0 + i] = c;
+        }
+        if ((tid & 31) == 0) ml_put_bits(out.bits, e0 + i, hm);
     }
 }
 
-// Bitonic network over 32 * E keys held E per lane (key index = r * 32 + lane): strides >= 32 pair two
-// registers of one lane, smaller strides pair two lanes through a shuffle.  No shared memory, no barrier.
-// The (size, stride) loops stay rolled -- fully unrolled, the E = 16 network alone is ~6000 instructions
-// and the kernel stalled on instruction fetch (ncu: no_instruction 33 cycles per issue) -- so register
-// pairs are reached through one unrolled body per register stride.
-template <int E, int RS>
-__device__ __forceinline__ void ml_reg_stage(unsigned long long (&key)[E], uint32_t size) {
-#pragma unroll
-    for (int r = 0; r < E; ++r) {
-        if (r & RS) continue;
-        const bool up = (((uint32_t)r * 32u) & size) == 0u;       // size > stride >= 32: a register-index bit
-        const unsigned long long a = key[r], b = key[r | RS];
-        const bool sw = (a > b) == up;
-        key[r] = sw ? b : a;
-        key[r | RS] = sw ? a : b;
+// ---- one warp, one bucket: keys in registers -----------------------------------------------------------------
+// Bitonic network over 32 * E keys held E per lane (key index = r * 32 + lane): strides >= 32 pair two registers of one
+// lane, smaller strides pair two lanes through a shuffle.  No shared memory, no barrier.  (Earlier versions, config-3
+// scale: windows of ~8 whole buckets sorted per CTA in shared memory, 40 ms; one warp per bucket in shared memory,
+// 31.5 ms at 36 % issue -- every stage waits for a shared-memory round trip.)
+//
+// E is a RUN-TIME value.  Round 1 instantiated loads, network and stores for E = 1, 2, 4, 8, 16: 5184 SASS
+// instructions, 83 KB, and since the warps of an SM work on buckets of different sizes at the same time the
+// instruction caches thrashed (ncu: sm__icc_request_hit_rate 87.8 %, gcc__cache_requests_type_instruction at 91.6 % of
+// peak, no_instruction 16 % of the stall samples) -- which is also why every variant that ADDED code (a
+// three-buckets-ahead prefetch loop, batched loads) got slower.  Now the keys sit in EMAX register pairs, registers
+// >= E are never touched, and the per-register work is skipped by warp-uniform branches over the register groups
+// {0}, {1}, {2, 3}, {4..7}, {8..15}; the (size, stride) loops stay rolled.  2424 instructions for EMAX = 16;
+// 17.5 -> 15.6 ms.  profiles/r02_k31_bucket_sort_experiments.txt has all of it.
+template <int R> struct MlRc { static constexpr int value = R; };
+template <int EMAX, typename F>
+__device__ __forceinline__ void ml_for_regs(uint32_t E, F f) {
+    f(MlRc<0>());
+    if constexpr (EMAX > 1) if (E > 1) {
+        f(MlRc<1>());
+        if constexpr (EMAX > 2) if (E > 2) {
+            f(MlRc<2>()); f(MlRc<3>());
+            if constexpr (EMAX > 4) if (E > 4) {
+                f(MlRc<4>()); f(MlRc<5>()); f(MlRc<6>()); f(MlRc<7>());
+                if constexpr (EMAX > 8) if (E > 8) {
+                    f(MlRc<8>()); f(MlRc<9>()); f(MlRc<10>()); f(MlRc<11>());
+                    f(MlRc<12>()); f(MlRc<13>()); f(MlRc<14>()); f(MlRc<15>());
+                }
+            }
+        }
     }
 }
 
-template <int E>
-__device__ __forceinline__ void ml_warp_bitonic(unsigned long long (&key)[E], int lane) {
+// stride 32 * RS pairs registers (r, r | RS); ascending where (r & s5) == 0, s5 = size / 32
+template <int EMAX, int RS>
+__device__ __forceinline__ void ml_reg_stage(unsigned long long (&key)[EMAX], uint32_t s5, uint32_t E) {
+    ml_for_regs<EMAX>(E, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
+        if constexpr ((r & RS) != 0) {              // visited as the upper register of its pair: E > r > r ^ RS
+            constexpr int lo = r ^ RS;
+            const bool up = ((uint32_t)lo & s5) == 0u;
+            const unsigned long long a = key[lo], b = key[r];
+            const bool sw = (a > b) == up;
+            key[lo] = sw ? b : a;
+            key[r] = sw ? a : b;
+        }
+    });
+}
+
+template <int EMAX>
+__device__ __forceinline__ void ml_warp_bitonic(unsigned long long (&key)[EMAX], uint32_t E, int lane) {
+    const uint32_t n = 32u * E;
 #pragma unroll 1
-    for (uint32_t size = 2; size <= 32u * E; size <<= 1) {
+    for (uint32_t size = 2; size <= n; size <<= 1) {
+        const uint32_t s5 = size >> 5;
+        // bit r set: register r's block descends at this size (size < 32: the same for all registers of a lane)
+        const uint32_t dn = size < 32u ? (((uint32_t)lane & size) ? 0xffffu : 0u)
+                                       : (s5 == 1u ? 0xaaaau : s5 == 2u ? 0xccccu : s5 == 4u ? 0xf0f0u : s5 == 8u ? 0xff00u : 0u);
 #pragma unroll 1
         for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
             if (stride >= 32u) {
-                switch (stride >> 5) {
-                case 1: if (E > 1) ml_reg_stage<E, (E > 1 ? 1 : 0)>(key, size); break;
-                case 2: if (E > 2) ml_reg_stage<E, (E > 2 ? 2 : 0)>(key, size); break;
-                case 4: if (E > 4) ml_reg_stage<E, (E > 4 ? 4 : 0)>(key, size); break;
-                default: if (E > 8) ml_reg_stage<E, (E > 8 ? 8 : 0)>(key, size); break;
-                }
-            } else if (size < 32u) {
-                // direction and side depend on the lane only: one predicate for all registers
-                const bool keep_min = (((uint32_t)lane & stride) == 0u) == (((uint32_t)lane & size) == 0u);
-#pragma unroll
-                for (int r = 0; r < E; ++r) {
-                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[r], (int)stride);
-                    key[r] = ((key[r] < o) == keep_min) ? key[r] : o;
-                }
+                const uint32_t rs = stride >> 5;
+                if (rs == 1u) { if constexpr (EMAX > 1) ml_reg_stage<EMAX, 1>(key, s5, E); }
+                else if (rs == 2u) { if constexpr (EMAX > 2) ml_reg_stage<EMAX, 2>(key, s5, E); }
+                else if (rs == 4u) { if constexpr (EMAX > 4) ml_reg_stage<EMAX, 4>(key, s5, E); }
+                else { if constexpr (EMAX > 8) ml_reg_stage<EMAX, 8>(key, s5, E); }
             } else {
-                // direction depends on the register index only: bit r of dn is set where the run descends
-                const bool lower = ((uint32_t)lane & stride) == 0u;
-                uint32_t dn = 0;
-#pragma unroll
-                for (int r = 0; r < E; ++r) dn |= (((uint32_t)r * 32u) & size) ? (1u << r) : 0u;
-#pragma unroll
-                for (int r = 0; r < E; ++r) {
+                // keep the smaller key where (lower lane of the pair) != (descending block)
+                const uint32_t mx = ((uint32_t)lane & stride) ? ~dn : dn;      // bit r set: keep the LARGER key
+                ml_for_regs<EMAX>(E, [&](auto rc) {
+                    constexpr int r = decltype(rc)::value;
                     const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[r], (int)stride);
-                    const bool keep_min = lower != (bool)((dn >> r) & 1u);
-                    key[r] = ((key[r] < o) == keep_min) ? key[r] : o;
-                }
+                    const bool keep_max = (mx >> r) & 1u;
+                    key[r] = ((key[r] > o) == keep_max) ? key[r] : o;
+                });
             }
         }
     }
 }
 
-// Sorts bucket [e0, e0 + m) (m <= 32 * E) on (suffix, position) and writes its records.  Key = suffix of the
-// code below the 22-bit prefix << 9 | index in the bucket: the index keeps equal codes in position order
-// and finds the position again afterwards (the bucket's positions ascend).
-template <int E>
+// Sorts bucket [e0, e0 + m) (m <= 32 * EMAX) on (suffix, position) and writes it.  Key = suffix of the code below the
+// 22-bit prefix << 9 | index in the bucket: the index keeps equal codes in position order and finds the position
+// again afterwards (the bucket's positions ascend).
+// The key build goes register by register -- position, then its packed words: 2 E dependent trips to memory, every
+// one a long_scoreboard stall in ncu's source page.  Overlapping them inside the warp (all positions first, the packed
+// words of four registers at a time) was measured twice and never won (13.3 vs 13.2-14.4 ms per class layout); what
+// did win was more warps per SM -- see ml_class_sort_kernel.
+template <int EMAX>
 __device__ __forceinline__ void ml_sort_bucket(const unsigned long long *__restrict__ packed,
                                                const uint32_t *__restrict__ pos_in, uint32_t e0, uint32_t m, int k,
-                                               unsigned long long prefix, int lane, uint4 *__restrict__ out,
-                                               uint32_t *__restrict__ heads) {
+                                               unsigned long long prefix, int lane, const MlOut &out) {
+    const uint32_t E = m <= 32u ? 1u : m <= 64u ? 2u : m <= 128u ? 4u : m <= 256u ? 8u : 16u;   // <= EMAX (caller)
     const int sb = 2 * k - kMsd3MaxBits;                       // suffix bits, <= 40
     const unsigned long long smask = (1ULL << sb) - 1ULL;
-    unsigned long long key[E];
-#if ML_CFG_LB == 0
-    // register by register: position, then its packed words.  The compiler keeps that order (2 E dependent trips to
-    // memory per bucket, all of them long_scoreboard stalls in ncu's source page) -- and it is the FASTER form: see
-    // the batched one below.
-#pragma unroll
-    for (int r = 0; r < E; ++r) {
+    unsigned long long key[EMAX];
+    ml_for_regs<EMAX>(E, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
         const uint32_t i = r * 32 + lane;
-#ifdef ML_FAKE_GATHER   /* experiment: no access to the packed store at all, keys from a hash of the position */
-        key[r] = i < m ? (((mix64(__ldcs(pos_in + e0 + i)) & smask) << 9) | i) : ~0ULL;
-#else
-        key[r] = i < m ? (((ml_code_at(packed, __ldcs(pos_in + e0 + i), k) & smask) << 9) | i) : ~0ULL;
-#endif
-    }
-#else
-    // Loads in batches, every batch's loads independent of each other: first the positions of all E registers, then
-    // -- ML_LB registers at a time -- both packed words of every position, then the keys.  Measured SLOWER at config 3
-    // (18.4-19.4 ms for batches of 2, 4, 8 against 16.4 ms): more gathers in flight do not help a kernel whose
-    // gathers already run at what the DRAM gives for random 64-byte lines (profiles/r02_k31_bucket_sort_experiments.txt).
-    constexpr int ML_LB = E < ML_CFG_LB ? E : ML_CFG_LB;
-    {
-        uint32_t p[E];
-#pragma unroll
-        for (int r = 0; r < E; ++r) {
-            const uint32_t i = r * 32 + lane;
-            p[r] = i < m ? pos_in[e0 + i] : 0u;                // position 0: a harmless, hot line for the padding lanes
-        }
-#pragma unroll
-        for (int r0 = 0; r0 < E; r0 += ML_LB) {
-            unsigned long long w0[ML_LB], w1[ML_LB];
-#pragma unroll
-            for (int q = 0; q < ML_LB; ++q) {
-                const unsigned long long *src = packed + (p[r0 + q] >> 5);
-                w0[q] = src[0];
-                w1[q] = src[1];                                // the store has a word of slack behind the last residue
-            }
-#pragma unroll
-            for (int q = 0; q < ML_LB; ++q) {
-                const uint32_t i = (r0 + q) * 32 + lane, off = p[r0 + q] & 31u;
-                // window of 32 residues at `off` of the 64 in (w0, w1); a shift by 64 is split in two
-                const unsigned long long hi = (w0[q] << (2 * off)) | ((w1[q] >> 1) >> (63 - 2 * off));
-                key[r0 + q] = i < m ? ((((hi >> (64 - 2 * k)) & smask) << 9) | i) : ~0ULL;
-            }
-        }
-    }
-#endif
-#ifndef ML_NO_SORT      /* experiment: everything but the network (output unsorted) */
-    ml_warp_bitonic<E>(key, lane);
-#endif
-    // the positions of the sorted records, all loads first (the bucket's slice of pos_in was read a moment ago)
-    uint32_t pv[E];
-#pragma unroll
-    for (int r = 0; r < E; ++r) pv[r] = (uint32_t)(r * 32 + lane) < m ? pos_in[e0 + (uint32_t)(key[r] & 511u)] : 0u;
+        key[r] = i < m ? (((ml_code_at(packed, pos_in[e0 + i], k) & smask) << 9) | i) : ~0ULL;
+    });
+    ml_warp_bitonic<EMAX>(key, E, lane);
     // a record starts a row when its code differs from its predecessor's (the first of a bucket always does)
     unsigned long long carry = ~0ULL;                          // suffix of key index r * 32 - 1
-#pragma unroll
-    for (int r = 0; r < E; ++r) {
+    ml_for_regs<EMAX>(E, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
         const uint32_t i = r * 32 + lane;
         const unsigned long long sfx = key[r] >> 9;
         unsigned long long prev = __shfl_up_sync(0xffffffffu, sfx, 1);
         if (lane == 0) prev = carry;
         carry = __shfl_sync(0xffffffffu, sfx, 31);
-        if (i < m) {
-            const unsigned long long c = (prefix << sb) | sfx;
-            __stcs(out + e0 + i, make_uint4((uint32_t)c, (uint32_t)(c >> 32), pv[r], 0u));
-            __stcs(heads + e0 + i, (i == 0 || sfx != prev) ? 1u : 0u);
+        const bool ok = i < m;
+        const uint32_t hm = __ballot_sync(0xffffffffu, ok && (i == 0 || sfx != prev));
+        if (ok) {
+            __stcs(out.pos + e0 + i, pos_in[e0 + (uint32_t)(key[r] & 511u)]);
+            __stcs(out.code + e0 + i, (prefix << sb) | sfx);
         }
-    }
+        if (lane == 0) ml_put_bits(out.bits, e0 + r * 32, hm);
+    });
 }
 
-// One WARP per bucket (strided over the 4^11 buckets), keys in registers.  Buckets of more than 512 records
-// are appended to big[] for the CTA kernels below.  ctl[0] = overflow flag, ctl[1] = entries in big[].
-// (Earlier versions, config-3 scale: windows of ~8 whole buckets sorted per CTA in shared memory, 40 ms --
-// the network is log^2 in the window size and half of every window was padding; one warp per bucket in
-// shared memory, 31.5 ms at 36 % issue -- every stage waits for a shared-memory round trip.)
-template <bool PIPE>
-__global__ void __launch_bounds__(ML_THREADS, ML_CFG_MINB) ml_bucket_sort_kernel(const unsigned long long *__restrict__ packed,
-                                                                    const uint32_t *__restrict__ pos_in,
-                                                                    const uint32_t *__restrict__ rowtab, uint32_t n_buckets,
-                                                                    int k, uint4 *__restrict__ out,
-                                                                    uint32_t *__restrict__ heads,
-                                                                    unsigned int *__restrict__ ctl, uint2 *__restrict__ big,
-                                                                    uint32_t big_cap) {
+// Buckets of (32 * ELO, 32 * EMAX] records, one WARP per bucket (strided over the 4^11 buckets); the other buckets are
+// left to the launches of the other classes.  Splitting by class buys occupancy: the kernel is bound by the latency
+// of its dependent loads, and what hides it is warps -- 3 CTAs per SM 19.0 ms, 4: 15.6, and a class of <= 256 records
+// needs only 16 key registers = 40 registers per thread = 6 CTAs per SM, one of <= 128 records 31 = 8 CTAs.
+// One launch for everything 15.6 ms, two classes 13.6, three 13.3 (config 3).  The class of the largest buckets
+// (EMAX = 16) also lists the buckets above 512 records in big[] for the CTA kernels below.
+// ctl[0] = overflow flag, ctl[1] = entries in big[].
+template <int ELO, int EMAX, int MINB>
+__global__ void __launch_bounds__(ML_THREADS, MINB) ml_class_sort_kernel(const unsigned long long *__restrict__ packed,
+                                                                        const uint32_t *__restrict__ pos_in,
+                                                                        const uint32_t *__restrict__ rowtab, uint32_t n_buckets,
+                                                                        int k, MlOut out, unsigned int *__restrict__ ctl,
+                                                                        uint2 *__restrict__ big, uint32_t big_cap) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t nw = gridDim.x * (ML_THREADS / 32);
-    auto sort_one = [&](uint32_t b, uint32_t e0, uint32_t m) {
-        if (m == 0) return;
-        if (m <= 32) ml_sort_bucket<1>(packed, pos_in, e0, m, k, b, lane, out, heads);
-        else if (m <= 64) ml_sort_bucket<2>(packed, pos_in, e0, m, k, b, lane, out, heads);
-        else if (m <= 128) ml_sort_bucket<4>(packed, pos_in, e0, m, k, b, lane, out, heads);
-        else if (m <= 256) ml_sort_bucket<8>(packed, pos_in, e0, m, k, b, lane, out, heads);
-        else if (m <= 512) ml_sort_bucket<16>(packed, pos_in, e0, m, k, b, lane, out, heads);
-        else if (lane == 0) {
+    for (uint32_t b = blockIdx.x * (ML_THREADS / 32) + w; b < n_buckets; b += nw) {
+        const uint32_t e0 = rowtab[b], m = rowtab[b + 1] - e0;
+        if (m <= 32u * ELO) continue;
+        if (m <= 32u * EMAX) ml_sort_bucket<EMAX>(packed, pos_in, e0, m, k, b, lane, out);
+        else if (EMAX == 16 && lane == 0) {
             const unsigned int slot = atomicAdd(&ctl[1], 1u);
             if (slot < big_cap) big[slot] = make_uint2(e0, e0 + m); else atomicOr(&ctl[0], 1u);
         }
-    };
-    const uint32_t b0 = blockIdx.x * (ML_THREADS / 32) + w;
-    if (!PIPE) {
-        for (uint32_t b = b0; b < n_buckets; b += nw) {
-            const uint32_t e0 = rowtab[b];
-            sort_one(b, e0, rowtab[b + 1] - e0);
-        }
-        return;
-    }
-    // A warp's bucket costs three dependent trips to memory -- its bounds, its positions, the packed words its
-    // positions point at (a random 64-byte line each) -- before the first compare; with 8 warps per scheduler that
-    // chain showed as long_scoreboard, the top stall (ncu: issue slots 53 % used).  So the warp works three buckets
-    // ahead of itself: while bucket i is sorted, the lines of bucket i + 1 are on their way to L2 (prefetch from the
-    // positions loaded one iteration earlier), the first ML_PF x 32 positions of bucket i + 2 are being loaded and so
-    // are the bounds of bucket i + 3.
-    constexpr int ML_PF = 4;
-    auto bounds = [&](uint32_t b, uint32_t &e, uint32_t &m) {
-        e = 0; m = 0;
-        if (b < n_buckets) { e = rowtab[b]; m = rowtab[b + 1] - e; }
-    };
-    auto fetch_pos = [&](uint32_t e, uint32_t m, uint32_t (&P)[ML_PF]) {
-#pragma unroll
-        for (int q = 0; q < ML_PF; ++q) P[q] = (uint32_t)(q * 32 + lane) < m ? pos_in[e + q * 32 + lane] : ~0u;
-    };
-    uint32_t e_c, m_c, e_1, m_1, e_2, m_2, P[ML_PF];
-    bounds(b0, e_c, m_c);
-    bounds(b0 + nw, e_1, m_1);
-    bounds(b0 + 2 * nw, e_2, m_2);
-    fetch_pos(e_1, m_1, P);
-    for (uint32_t b = b0; b < n_buckets; b += nw) {
-#pragma unroll
-        for (int q = 0; q < ML_PF; ++q)
-            if (P[q] != ~0u) asm volatile("prefetch.global.L2 [%0];" ::"l"(packed + (P[q] >> 5)));
-        fetch_pos(e_2, m_2, P);
-        uint32_t e_3, m_3;
-        bounds(b + 3 * nw, e_3, m_3);
-        sort_one(b, e_c, m_c);
-        e_c = e_1; m_c = m_1;
-        e_1 = e_2; m_1 = m_2;
-        e_2 = e_3; m_2 = m_3;
     }
 }
 
@@ -298,8 +266,7 @@ __global__ void __launch_bounds__(ML_THREADS, ML_CFG_MINB) ml_bucket_sort_kernel
 // size class and skips the others
 static constexpr int ML_MID = 2048, ML_BIG = 16384, ML_BIG_THREADS = 1024;
 __global__ void __launch_bounds__(ML_THREADS) ml_mid_bucket_kernel(const unsigned long long *__restrict__ packed,
-                                                                   const uint32_t *__restrict__ pos_in, int k,
-                                                                   uint4 *__restrict__ out, uint32_t *__restrict__ heads,
+                                                                   const uint32_t *__restrict__ pos_in, int k, MlOut out,
                                                                    unsigned int *__restrict__ ctl, const uint2 *__restrict__ big) {
     __shared__ unsigned long long key[ML_MID];
     __shared__ uint32_t val[ML_MID];
@@ -309,12 +276,11 @@ __global__ void __launch_bounds__(ML_THREADS) ml_mid_bucket_kernel(const unsigne
         if (threadIdx.x == 0) atomicAdd(&ctl[2], 1u);
         return;
     }
-    ml_sort_range<ML_THREADS>(packed, pos_in, r.x, cnt, k, key, val, out, heads);
+    ml_sort_range<ML_THREADS>(packed, pos_in, r.x, cnt, k, key, val, out);
 }
 
 __global__ void __launch_bounds__(ML_BIG_THREADS) ml_big_bucket_kernel(const unsigned long long *__restrict__ packed,
-                                                                       const uint32_t *__restrict__ pos_in, int k,
-                                                                       uint4 *__restrict__ out, uint32_t *__restrict__ heads,
+                                                                       const uint32_t *__restrict__ pos_in, int k, MlOut out,
                                                                        unsigned int *__restrict__ ctl, const uint2 *__restrict__ big) {
     extern __shared__ __align__(16) unsigned char ml_raw[];
     unsigned long long *key = reinterpret_cast<unsigned long long *>(ml_raw);
@@ -326,14 +292,14 @@ __global__ void __launch_bounds__(ML_BIG_THREADS) ml_big_bucket_kernel(const uns
         if (threadIdx.x == 0) atomicOr(&ctl[0], 1u);
         return;
     }
-    ml_sort_range<ML_BIG_THREADS>(packed, pos_in, r.x, cnt, k, key, val, out, heads);
+    ml_sort_range<ML_BIG_THREADS>(packed, pos_in, r.x, cnt, k, key, val, out);
 }
 
-// true: *sorted (= g->recA) holds the n records {code lo, code hi, position, 0} in (code, position) order and
-// *head_flags (= g->recB) one word per record: 1 where a row (a new code) starts
+// true: g->g_pos holds the n positions in (code, position) order, *codes (= g->recA) the code of every record in that
+// order and *head_bits (= g->ml_bits) bit i set where a row (a new code) starts at record i
 // staged: a pipelined ingest already ran the prefix sort up to pass 2 (or 3) for exactly these contigs.
-bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, bool staged, const uint4 **sorted,
-                   const uint32_t **head_flags) {
+bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, bool staged,
+                   const unsigned long long **codes, const unsigned int **head_bits) {
     cudaStream_t s = g->stream;
     const int k = g->k;
     const uint64_t n = hc.n_kmers;
@@ -341,12 +307,15 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     static const bool off = getenv("PDG_NO_MSDLONG") != nullptr;
     if (off || 2 * k <= kMsd3MaxBits || n == 0 || n >= (1ULL << 32)) return false;
     if (!staged) {
-        g->recA.reserve(n * 16, s);        // before the staging so that nothing is reallocated under it
         msd3_reserve(g, hc.pos0, hc.pos1, 1);
         msd3_stage_group(g, ct, hc.pos0, hc.pos1);
     }
     if (!g->m3_launched) msd3_finish_launch(g, /*rows=*/false);   // g_pos grouped by prefix, scratch0 = bucket starts (+ sentinel)
-    if (staged) g->recA.reserve(n * 16, s);   // pass 3 no longer reads recA; reserve() drains the stream before it frees
+    // recA (pass 1's output) and recB (pass 2's) are free once pass 3 is in the stream: the codes go to recA, the sorted
+    // positions to recB, which then changes places with g_pos.  (recA >= n * 8 and recB >= n * 8 bytes: msd3_reserve.)
+    const size_t n_words = (size_t)((n + 31) / 32) + 1;
+    g->ml_bits.reserve(n_words * 4, s);
+    PDG_CUDA(cudaMemsetAsync(g->ml_bits.p, 0, n_words * 4, s));
     // room for EVERY bucket (33.5 MB): with a fixed 2^18 entries, 500 genomes per GPU (config 4 on 2 GPUs: ~600
     // records per bucket, nearly all of the 4^11 buckets above the warp path's 512) overflowed the list and sent the
     // whole build to the 8-pass LSD sort of 16-byte records -- 282 ms for 5x the records of a 22 ms sort
@@ -362,31 +331,44 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
         PDG_CUDA(cudaFuncSetAttribute(ml_big_bucket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ML_BIG * 12));
         g->attr_mask |= pdg_graph::ATTR_MSDLONG;
     }
-    const unsigned grid = 148 * 16;                            // warps stride over the buckets
     const unsigned long long *packed = g->packed.as<unsigned long long>();
     const uint32_t *pos_in = g->g_pos.as<uint32_t>(), *rowtab = g->scratch0.as<uint32_t>();
-    uint4 *out = g->recA.as<uint4>();
-    uint32_t *heads = g->recB.as<uint32_t>();                  // free since pass 3; n * 4 <= n * 8 bytes
+    const MlOut out{g->recB.as<uint32_t>(), g->recA.as<unsigned long long>(), g->ml_bits.as<unsigned int>()};
     unsigned int *ctl = g->ml_flag.as<unsigned int>();
     uint2 *big = reinterpret_cast<uint2 *>(g->ml_flag.as<unsigned char>() + 16);
     // (an L2 persistence window over the packed store was tried for the random code gathers: the kernel
     // did not get faster and the rest of the step lost 16 ms to the limit / reset calls)
+    // PDG_ML_CLASSES: 1 = one launch for all bucket sizes (4 CTAs/SM), 2 = (<= 256 | <= 512), 3 = (<= 128 | <= 256 | <= 512)
+    static const int classes = getenv("PDG_ML_CLASSES") ? atoi(getenv("PDG_ML_CLASSES")) : ML_CFG_CLASSES;
+#define ML_LAUNCH(ELO, EMAX, MINB)                                                                                       \
+    do {                                                                                                                 \
+        ml_class_sort_kernel<ELO, EMAX, MINB><<<148 * MINB * 4, ML_THREADS, 0, s>>>(packed, pos_in, rowtab, n_buckets, k, \
+                                                                                   out, ctl, big, big_cap);           \
+        PDG_LAUNCHED(g);                                                                                                 \
+    } while (0)
     PDG_CUDA(cudaEventRecord(g->k_events[6], s));
-    // the three-buckets-ahead loop is measured SLOWER (20.8 against 16.4 ms at config 3): off unless asked for, kept for the A/B
-    static const bool pipe = getenv("PDG_ML_PIPE") && atoi(getenv("PDG_ML_PIPE")) != 0;
-    if (pipe) ml_bucket_sort_kernel<true><<<grid, ML_THREADS, 0, s>>>(packed, pos_in, rowtab, n_buckets, k, out, heads, ctl, big, big_cap);
-    else ml_bucket_sort_kernel<false><<<grid, ML_THREADS, 0, s>>>(packed, pos_in, rowtab, n_buckets, k, out, heads, ctl, big, big_cap);
-    PDG_LAUNCHED(g);
+    if (classes >= 3) {
+        ML_LAUNCH(0, 4, ML_CFG_MINB_A);
+        ML_LAUNCH(4, 8, 6);
+        ML_LAUNCH(8, 16, 4);
+    } else if (classes == 2) {
+        ML_LAUNCH(0, 8, 6);
+        ML_LAUNCH(8, 16, 4);
+    } else {
+        ML_LAUNCH(0, 16, 4);
+    }
+#undef ML_LAUNCH
+    g->stats.sort_kernel_launches = classes >= 3 ? 3 : classes == 2 ? 2 : 1;
     unsigned int h_ctl[4] = {0, 0, 0, 0};
     PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
     if (!h_ctl[0] && h_ctl[1]) {   // buckets too large for a warp: one CTA each
-        ml_mid_bucket_kernel<<<h_ctl[1], ML_THREADS, 0, s>>>(packed, pos_in, k, out, heads, ctl, big);
+        ml_mid_bucket_kernel<<<h_ctl[1], ML_THREADS, 0, s>>>(packed, pos_in, k, out, ctl, big);
         PDG_LAUNCHED(g);
         PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 12, cudaMemcpyDeviceToHost, s));
         PDG_CUDA(cudaStreamSynchronize(s));
         if (h_ctl[2]) {
-            ml_big_bucket_kernel<<<h_ctl[1], ML_BIG_THREADS, ML_BIG * 12, s>>>(packed, pos_in, k, out, heads, ctl, big);
+            ml_big_bucket_kernel<<<h_ctl[1], ML_BIG_THREADS, ML_BIG * 12, s>>>(packed, pos_in, k, out, ctl, big);
             PDG_LAUNCHED(g);
             PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 4, cudaMemcpyDeviceToHost, s));
         }
@@ -403,8 +385,7 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
         // back to back on this stream (a pipelined ingest interleaves them with the copies)
         float msw = 0.f;
         cudaEventElapsedTime(&msw, g->k_events[6], g->k_events[7]);
-        g->stats.ms_sort_kernel_avg = msw;
-        g->stats.sort_kernel_launches = 1;
+        g->stats.ms_sort_kernel_avg = msw;        // all classes together
     }
     if (g->m3_timed && !staged) {
         float ms[5] = {0, 0, 0, 0, 0};
@@ -418,8 +399,11 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     g->stats.sort_passes = 4;
     g->stats.sort_records = n;
     g->stats.sort_groups = n_groups;
-    *sorted = out;
-    *head_flags = heads;
+    // the sorted position column is the index's: the two buffers change places (both hold >= n * 4 bytes)
+    std::swap(g->g_pos.p, g->recB.p);
+    std::swap(g->g_pos.cap, g->recB.cap);
+    *codes = g->recA.as<unsigned long long>();
+    *head_bits = g->ml_bits.as<unsigned int>();
     return true;
 }
 

@@ -17,10 +17,10 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "mlbase": (256, 8, 5),                               # k > 16 bucket sort as shipped
-    "mlfake": (256, 8, 5, "-DML_FAKE_GATHER"),           # experiment: keys from a hash of the position, no gather (wrong output)
-    "mlnosort": (256, 8, 5, "-DML_NO_SORT"),             # experiment: gather and write, no sorting network (wrong output)
-    "mlfakenosort": (256, 8, 5, "-DML_FAKE_GATHER", "-DML_NO_SORT"),   # streaming part only
+    "mlser": (256, 8, 5),                                        # k > 16 bucket sort, loads one register at a time
+    "mllb4": (256, 8, 5, "-DML_CFG_LB=4"),                       # loads in batches of four registers
+    "mllb4a6": (256, 8, 5, "-DML_CFG_LB=4", "-DML_CFG_MINB_A=6"),  # ... and the small class at 6 CTAs/SM (no spills)
+    "mlsera6": (256, 8, 5, "-DML_CFG_MINB_A=6"),
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
 
