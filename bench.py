@@ -526,10 +526,12 @@ def kernel_table(st, k, peak):
         add("m3_hist_kernel (joint digit histograms from the packed genome)", st["ms_hist"], n, 0.25)
     if k > 16 and st["sort_passes"] == 4 and st["ms_sort_kernel_avg"] > 0:
         # (also when the prefix passes ran inside a pipelined ingest and have no event times of their own)
-        # reads a position, gathers the two packed words of its code, writes the position, the 8-byte code and one
-        # row-head bit; the launches of all bucket-size classes (+ the CTA kernels of the few big buckets) timed together
-        add("ml_class_sort_kernel (prefix buckets -> position column, codes, row-head bits; all size classes)",
-            st["ms_sort_kernel_avg"], n, 32.125)
+        # per record: reads a position, gathers the two packed words of its code, writes the position; per ROW (distinct
+        # code of this rank): writes the code and the record index of its head.  The launches of all bucket-size classes
+        # (+ the CTA kernels of the few big buckets) are timed together.
+        rows_per_record = float(st["n_nodes"]) / n if st.get("n_nodes") else 0.0
+        add("ml_class_sort_kernel (prefix buckets -> position column + the rows' codes and starts; all size classes)",
+            st["ms_sort_kernel_avg"], n, 24.0 + 12.0 * rows_per_record)
     elif st["ms_pass"][0] <= 0 and st["ms_sort_kernel_avg"] > 0:
         add("onesweep_kernel (one LSD partition pass)", st["ms_sort_kernel_avg"], n, 16.0 if k <= 16 else 32.0)
     add("fb_summ_kernel (FASTA bytes -> tile summaries)", st["ms_ingest_a"], nb, 1.0)

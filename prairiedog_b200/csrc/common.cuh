@@ -158,7 +158,6 @@ struct pdg_graph {
     pdg::DevBuf m3_tile_info, m3_gbase;   // msd3.cu: per-tile contig info; per-group cell bases + record offsets
     struct M3Group { uint64_t pos0, pos1, rec_off; };
     pdg::DevBuf ml_flag;                 // msdlong.cu: overflow flag + list of the buckets too large for a warp
-    pdg::DevBuf ml_bits;                 // msdlong.cu: one bit per sorted record, set where a row starts
     bool m3_launched = false;            // msd3_finish_launch ran for the staged groups
     std::vector<M3Group> m3_groups;      // groups staged since msd3_reserve
     uint32_t m3_max_groups = 0;

@@ -77,42 +77,6 @@ static void rows_from_sorted(pdg_graph *g, const Rec *sorted, uint64_t n, const 
     PDG_LAUNCHED(g);
 }
 
-// ---- rows from one head bit per sorted record (msdlong.cu) ------------------------------------------------
-// Row id of the head at record i = heads before i = (prefix of the word popcounts)[i / 32] + popcount of the lower bits
-// of its word: the scan runs over n / 32 words instead of n flags, and only heads touch the code column.
-__global__ void g_rows_bits_kernel(const unsigned long long *__restrict__ code, const unsigned int *__restrict__ bits,
-                                   const uint32_t *__restrict__ wrank, uint64_t n, uint64_t *__restrict__ codes,
-                                   uint32_t *__restrict__ rowptr) {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t wd = bits[i >> 5], b = (uint32_t)i & 31u;
-    if ((wd >> b) & 1u) {
-        const uint32_t id = wrank[i >> 5] + __popc(wd & ((1u << b) - 1u));
-        codes[id] = code[i];
-        rowptr[id] = (uint32_t)i;
-    }
-    if (i == n - 1) rowptr[wrank[(n + 31) >> 5]] = (uint32_t)n;
-}
-
-static void rows_from_head_bits(pdg_graph *g, const unsigned long long *code, const unsigned int *bits, uint64_t n) {
-    cudaStream_t s = g->stream;
-    const uint64_t nw = (n + 31) / 32;
-    g->scratch1.reserve((2 * nw + 2) * 4, s);
-    uint32_t *cnt = g->scratch1.as<uint32_t>(), *wrank = cnt + nw;
-    g_popc_words_kernel<<<grid_for(nw, 256), 256, 0, s>>>(bits, nw, cnt);
-    PDG_LAUNCHED(g);
-    exclusive_scan_u32_u32(cnt, wrank, nw, g);
-    uint32_t nn = 0;
-    PDG_CUDA(cudaMemcpyAsync(&nn, wrank + nw, 4, cudaMemcpyDeviceToHost, s));
-    PDG_CUDA(cudaStreamSynchronize(s));
-    g->g_nodes = nn;
-    g->g_codes.reserve(std::max<size_t>((size_t)nn * 8, 16), s);
-    g->g_rowptr.reserve(((size_t)nn + 1) * 4, s);
-    g_rows_bits_kernel<<<grid_for(n, 256), 256, 0, s>>>(code, bits, wrank, n, g->g_codes.as<uint64_t>(),
-                                                       g->g_rowptr.as<uint32_t>());
-    PDG_LAUNCHED(g);
-}
-
 void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, int flags) {
     cudaStream_t s = g->stream;
     const int k = g->k;
@@ -127,7 +91,6 @@ void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, i
     if (n == 0) return;
     TraverseOut out;
     uint64_t passes = 0;
-    const unsigned int *ml_heads = nullptr;
     g->collect_sort_stats = true;
     // a pipelined ingest already ran passes 1-2 (and launched pass 3) group by group -- if the caller
     // declared exactly the contigs it assumed, only the rest is left
@@ -144,8 +107,7 @@ void build_g_index(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, i
         }
         else if (!ksort_build(g, ct, hc, &sorted)) rows_from_sorted<uint64_t>(g, sorted, n);
         passes = g->stats.sort_passes;
-    } else if (const unsigned long long *srt = nullptr; !(flags & PDG_F_FORCE_SORT_NODES) && msdlong_build(g, ct, hc, staged, &srt, &ml_heads)) {
-        rows_from_head_bits(g, srt, ml_heads, n);       // msdlong.cu: prefix MSD + bucket sort; g_pos is already final
+    } else if (!(flags & PDG_F_FORCE_SORT_NODES) && msdlong_build(g, ct, hc, staged)) {   // msdlong.cu: prefix MSD + bucket sort + rows
         passes = g->stats.sort_passes;
     } else {
         g->recA.reserve(n * 16, s);

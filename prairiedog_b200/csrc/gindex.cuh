@@ -51,11 +51,10 @@ void msd3_finish_launch(pdg_graph *g, bool rows = true);                 // pass
 void msd3_finish_complete(pdg_graph *g, uint64_t n_kmers);
 void msd3_finish(pdg_graph *g, uint64_t n_kmers);      // launch (unless already launched) + complete
 
-// msdlong.cu: 17 <= k <= 31: msd3 on the 11-residue prefix + a sort of every bucket in registers; on success g->g_pos
-// is the sorted position column, *codes the code of every sorted record, *head_bits one bit per record (row starts);
+// msdlong.cu: 17 <= k <= 31: msd3 on the 11-residue prefix + a sort of every bucket in registers; on success the
+// occurrence index (g_pos, g_codes, g_rowptr, g_nodes) is complete;
 // false = not applicable / a bucket did not fit (the caller runs the LSD sort of radix.cu)
-bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, bool staged,
-                   const unsigned long long **codes, const unsigned int **head_bits);
+bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, bool staged);
 
 // xbuild.cu: builds the explicit part from g->x_* plus the demoted contigs
 void build_x_part(pdg_graph *g, const HostContigs &demoted);

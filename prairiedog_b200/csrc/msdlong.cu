@@ -22,29 +22,28 @@ static constexpr int ML_THREADS = 256;
 #ifndef ML_CFG_CLASSES
 #define ML_CFG_CLASSES 3   /* launches of the bucket sort by bucket-size class (see ml_class_sort_kernel); 1, 2 or 3 */
 #endif
+#ifndef ML_CFG_MIRROR
+#define ML_CFG_MIRROR 1    /* class of 257-512 records: the network that skips its padding registers (ml_sort_bucket_c) */
+#endif
 #ifndef ML_CFG_MINB_A
 #define ML_CFG_MINB_A 8    /* CTAs per SM of the class of buckets <= 128 records */
 #endif
 
-// What a bucket sort writes for record i of the sorted order (i = bucket start + rank inside the bucket, which IS the
-// record's final index: the buckets are in prefix order): its position, its full code, and bit i of `bits` when a row
-// (a new code) starts at i.  bits is zeroed before the launches; buckets do not end on word boundaries, so the bits go
-// in with atomicOr.  (Until round 2 the kernels wrote 16-byte {code, position} records plus one 32-bit flag per
-// record, and gbuild.cu made the rows with a scan over the 5e8 flags and a pass over the 8 GB of records: 5.5 ms of a
-// 27 ms step at config 3, profiles/r02_launches_k31_classes.csv.)
+// What a bucket sort writes.  Record i of the sorted order (i = bucket start + rank inside the bucket, which IS the
+// record's final index: the buckets are in prefix order) gets its position in pos[i].  The HEADS of the bucket -- the
+// records at which a row (a new code) starts -- are written densely from the bucket's start: hcode[e0 + j] and
+// hidx[e0 + j] are the code and the record index of the bucket's j-th row, cnt[b] the number of rows of bucket b.
+// ml_rows_kernel then copies them to their global row ids (an exclusive scan over the 4^11 bucket counts).
+// (Until round 2 the kernels wrote 16-byte {code, position} records plus one 32-bit flag per record, and gbuild.cu
+// made the rows with a scan over the 5e8 flags and a pass over the 8 GB of records: 5.5 ms of a 27 ms step at
+// config 3, profiles/r02_launches_k31_classes.csv.  A first fix -- code of every record + one head BIT per record,
+// rows by a popcount scan -- still spent 2.1 ms picking the heads' codes out of 4 GB, r02_launches_k31_final.csv.)
 struct MlOut {
     uint32_t *pos;
-    unsigned long long *code;
-    unsigned int *bits;
+    unsigned long long *hcode;
+    uint32_t *hidx;
+    uint32_t *cnt;
 };
-
-// head bits of the 32 records that start at index g0 (bit l = record g0 + l); called by one lane
-__device__ __forceinline__ void ml_put_bits(unsigned int *__restrict__ bits, uint32_t g0, uint32_t mask) {
-    if (!mask) return;
-    const uint32_t sh = g0 & 31u;
-    atomicOr(&bits[g0 >> 5], mask << sh);
-    if (sh && (mask >> (32u - sh))) atomicOr(&bits[(g0 >> 5) + 1], mask >> (32u - sh));
-}
 
 __device__ __forceinline__ unsigned long long ml_code_at(const unsigned long long *__restrict__ packed, uint32_t p, int k) {
     const uint32_t w = p >> 5, off = p & 31u;
@@ -69,7 +68,8 @@ __device__ __forceinline__ uint32_t ml_first_bucket(const uint32_t *__restrict__
 template <int THREADS>
 __device__ __forceinline__ void ml_sort_range(const unsigned long long *__restrict__ packed,
                                               const uint32_t *__restrict__ pos_in, uint32_t e0, uint32_t cnt, int k,
-                                              unsigned long long *key, uint32_t *val, const MlOut &out) {
+                                              unsigned long long *key, uint32_t *val, const MlOut &out,
+                                              uint32_t bucket) {
     const int tid = threadIdx.x;
     uint32_t tn = 2;           // sort the next power of two >= cnt
     while (tn < cnt) tn <<= 1;
@@ -101,17 +101,23 @@ __device__ __forceinline__ void ml_sort_range(const unsigned long long *__restri
         }
     }
     __syncthreads();
-    for (uint32_t i0 = 0; i0 < cnt; i0 += THREADS) {     // whole warps: the ballot needs every lane
-        const uint32_t i = i0 + tid;
-        const bool ok = i < cnt;
-        const unsigned long long c = ok ? key[i] : 0ULL;
-        const bool head = ok && (i == 0 || c != key[i - 1]);     // a bucket is a whole number of rows
-        const uint32_t hm = __ballot_sync(0xffffffffu, head);
-        if (ok) {
-            out.pos[e0 + i] = val[i];
-            out.code[e0 + i] = c;
+    for (uint32_t i = tid; i < cnt; i += THREADS) out.pos[e0 + i] = val[i];
+    if (tid < 32) {     // the rows of the bucket, in order, by one warp (these buckets are rare)
+        uint32_t rows = 0;
+        for (uint32_t i0 = 0; i0 < cnt; i0 += 32) {
+            const uint32_t i = i0 + tid;
+            const bool ok = i < cnt;
+            const unsigned long long c = ok ? key[i] : 0ULL;
+            const bool head = ok && (i == 0 || c != key[i - 1]);     // a bucket is a whole number of rows
+            const uint32_t hm = __ballot_sync(0xffffffffu, head);
+            if (head) {
+                const uint32_t j = rows + __popc(hm & ((1u << tid) - 1u));
+                out.hcode[e0 + j] = c;
+                out.hidx[e0 + j] = e0 + i;
+            }
+            rows += __popc(hm);
         }
-        if ((tid & 31) == 0) ml_put_bits(out.bits, e0 + i, hm);
+        if (tid == 0) out.cnt[bucket] = rows;
     }
 }
 
@@ -218,6 +224,7 @@ __device__ __forceinline__ void ml_sort_bucket(const unsigned long long *__restr
     ml_warp_bitonic<EMAX>(key, E, lane);
     // a record starts a row when its code differs from its predecessor's (the first of a bucket always does)
     unsigned long long carry = ~0ULL;                          // suffix of key index r * 32 - 1
+    uint32_t rows = 0;                                         // rows of the bucket so far
     ml_for_regs<EMAX>(E, [&](auto rc) {
         constexpr int r = decltype(rc)::value;
         const uint32_t i = r * 32 + lane;
@@ -225,14 +232,149 @@ __device__ __forceinline__ void ml_sort_bucket(const unsigned long long *__restr
         unsigned long long prev = __shfl_up_sync(0xffffffffu, sfx, 1);
         if (lane == 0) prev = carry;
         carry = __shfl_sync(0xffffffffu, sfx, 31);
-        const bool ok = i < m;
-        const uint32_t hm = __ballot_sync(0xffffffffu, ok && (i == 0 || sfx != prev));
-        if (ok) {
-            __stcs(out.pos + e0 + i, pos_in[e0 + (uint32_t)(key[r] & 511u)]);
-            __stcs(out.code + e0 + i, (prefix << sb) | sfx);
+        const bool ok = i < m, head = ok && (i == 0 || sfx != prev);
+        const uint32_t hm = __ballot_sync(0xffffffffu, head);
+        if (ok) __stcs(out.pos + e0 + i, pos_in[e0 + (uint32_t)(key[r] & 511u)]);
+        if (head) {
+            const uint32_t j = rows + __popc(hm & ((1u << lane) - 1u));
+            __stcs(out.hcode + e0 + j, (prefix << sb) | sfx);
+            __stcs(out.hidx + e0 + j, e0 + i);
         }
-        if (lane == 0) ml_put_bits(out.bits, e0 + r * 32, hm);
+        rows += __popc(hm);
     });
+    if (lane == 0) out.cnt[prefix] = rows;      // prefix = the bucket's number
+}
+
+// ---- the class of 257-512 records: a network that skips its padding ------------------------------------------
+// A bucket of 300 records needs 10 key registers per lane, the bitonic network above a power of two: 16, of which 6
+// hold nothing but +inf.  In the form of the network whose comparators ALL put the smaller key at the lower index (the
+// first step of every merge pairs i with its mirror image i ^ (size - 1) instead of i ^ (size / 2)), a +inf at the top
+// never moves, so every comparator that touches a register >= E can be left out: the 45 stages of n = 512 run over
+// E2 = E rounded up to even (10, 12, 14, 16) registers.  The mirror step pairs register r with r ^ (size / 32 - 1) of
+// the lane ^ 31; both keys of a pair are fetched before either is replaced.
+__device__ __forceinline__ unsigned long long ml_min64(unsigned long long a, unsigned long long b) { return a < b ? a : b; }
+__device__ __forceinline__ unsigned long long ml_max64(unsigned long long a, unsigned long long b) { return a < b ? b : a; }
+
+// f(r) for the registers in use: 0..9 always (E2 >= 10), then pair by pair
+template <typename F>
+__device__ __forceinline__ void ml_for_regs_c(uint32_t E2, F f) {
+    f(MlRc<0>()); f(MlRc<1>()); f(MlRc<2>()); f(MlRc<3>()); f(MlRc<4>()); f(MlRc<5>()); f(MlRc<6>()); f(MlRc<7>());
+    f(MlRc<8>()); f(MlRc<9>());
+    if (E2 > 10) {
+        f(MlRc<10>()); f(MlRc<11>());
+        if (E2 > 12) {
+            f(MlRc<12>()); f(MlRc<13>());
+            if (E2 > 14) { f(MlRc<14>()); f(MlRc<15>()); }
+        }
+    }
+}
+
+// mirror step of size 32 * S5 (S5 = 2, 4, 8, 16): (register a, lane) with (register a ^ (S5 - 1), lane ^ 31)
+template <int S5, int A>
+__device__ __forceinline__ void ml_mirror_pair(unsigned long long (&key)[16], uint32_t E2) {
+    constexpr int B = A ^ (S5 - 1);
+    if constexpr (A < B) {
+        if ((uint32_t)B < E2) {
+            const unsigned long long oa = __shfl_xor_sync(0xffffffffu, key[B], 31);
+            const unsigned long long ob = __shfl_xor_sync(0xffffffffu, key[A], 31);
+            key[A] = ml_min64(key[A], oa);
+            key[B] = ml_max64(key[B], ob);
+        }
+    }
+}
+template <int S5>
+__device__ __forceinline__ void ml_mirror_stage(unsigned long long (&key)[16], uint32_t E2) {
+    ml_mirror_pair<S5, 0>(key, E2); ml_mirror_pair<S5, 1>(key, E2); ml_mirror_pair<S5, 2>(key, E2); ml_mirror_pair<S5, 3>(key, E2);
+    ml_mirror_pair<S5, 4>(key, E2); ml_mirror_pair<S5, 5>(key, E2); ml_mirror_pair<S5, 6>(key, E2); ml_mirror_pair<S5, 7>(key, E2);
+    ml_mirror_pair<S5, 8>(key, E2); ml_mirror_pair<S5, 9>(key, E2); ml_mirror_pair<S5, 10>(key, E2); ml_mirror_pair<S5, 11>(key, E2);
+    ml_mirror_pair<S5, 12>(key, E2); ml_mirror_pair<S5, 13>(key, E2); ml_mirror_pair<S5, 14>(key, E2); ml_mirror_pair<S5, 15>(key, E2);
+}
+
+// stride 32 * RS: registers (a, a | RS) of one lane, smaller key to a
+template <int RS, int A>
+__device__ __forceinline__ void ml_up_pair(unsigned long long (&key)[16], uint32_t E2) {
+    if constexpr ((A & RS) == 0) {
+        constexpr int B = A | RS;
+        if ((uint32_t)B < E2) {
+            const unsigned long long a = key[A], b = key[B];
+            key[A] = ml_min64(a, b);
+            key[B] = ml_max64(a, b);
+        }
+    }
+}
+template <int RS>
+__device__ __forceinline__ void ml_up_stage(unsigned long long (&key)[16], uint32_t E2) {
+    ml_up_pair<RS, 0>(key, E2); ml_up_pair<RS, 1>(key, E2); ml_up_pair<RS, 2>(key, E2); ml_up_pair<RS, 3>(key, E2);
+    ml_up_pair<RS, 4>(key, E2); ml_up_pair<RS, 5>(key, E2); ml_up_pair<RS, 6>(key, E2); ml_up_pair<RS, 7>(key, E2);
+    ml_up_pair<RS, 8>(key, E2); ml_up_pair<RS, 9>(key, E2); ml_up_pair<RS, 10>(key, E2); ml_up_pair<RS, 11>(key, E2);
+    ml_up_pair<RS, 12>(key, E2); ml_up_pair<RS, 13>(key, E2); ml_up_pair<RS, 14>(key, E2); ml_up_pair<RS, 15>(key, E2);
+}
+
+// all 512 (virtual) keys ascending; registers >= E2 do not exist
+__device__ __forceinline__ void ml_warp_sort_c(unsigned long long (&key)[16], uint32_t E2, int lane) {
+    // lanes: exchange with lane ^ x, the lower lane of the pair (bit `lowbit` clear) keeps the smaller key
+    auto lane_stage = [&](uint32_t x, uint32_t lowbit) {
+        const bool lower = ((uint32_t)lane & lowbit) == 0u;
+        ml_for_regs_c(E2, [&](auto rc) {
+            constexpr int r = decltype(rc)::value;
+            const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[r], (int)x);
+            key[r] = ((key[r] < o) == lower) ? key[r] : o;
+        });
+    };
+#pragma unroll 1
+    for (uint32_t size = 2; size <= 512u; size <<= 1) {
+        if (size <= 32u) lane_stage(size - 1u, size >> 1);
+        else if (size == 64u) ml_mirror_stage<2>(key, E2);
+        else if (size == 128u) ml_mirror_stage<4>(key, E2);
+        else if (size == 256u) ml_mirror_stage<8>(key, E2);
+        else ml_mirror_stage<16>(key, E2);
+#pragma unroll 1
+        for (uint32_t stride = size >> 2; stride > 0; stride >>= 1) {
+            if (stride >= 32u) {
+                if (stride == 32u) ml_up_stage<1>(key, E2);
+                else if (stride == 64u) ml_up_stage<2>(key, E2);
+                else ml_up_stage<4>(key, E2);
+            } else {
+                lane_stage(stride, stride);
+            }
+        }
+    }
+}
+
+// bucket of 257..512 records (9 <= E <= 16 registers in use)
+__device__ __forceinline__ void ml_sort_bucket_c(const unsigned long long *__restrict__ packed,
+                                                 const uint32_t *__restrict__ pos_in, uint32_t e0, uint32_t m, int k,
+                                                 unsigned long long prefix, int lane, const MlOut &out) {
+    const uint32_t E2 = (((m + 31u) >> 5) + 1u) & ~1u;         // 10, 12, 14 or 16
+    const int sb = 2 * k - kMsd3MaxBits;
+    const unsigned long long smask = (1ULL << sb) - 1ULL;
+    unsigned long long key[16];
+    ml_for_regs_c(E2, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
+        const uint32_t i = r * 32 + lane;
+        key[r] = i < m ? (((ml_code_at(packed, pos_in[e0 + i], k) & smask) << 9) | i) : ~0ULL;
+    });
+    ml_warp_sort_c(key, E2, lane);
+    unsigned long long carry = ~0ULL;
+    uint32_t rows = 0;
+    ml_for_regs_c(E2, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
+        const uint32_t i = r * 32 + lane;
+        const unsigned long long sfx = key[r] >> 9;
+        unsigned long long prev = __shfl_up_sync(0xffffffffu, sfx, 1);
+        if (lane == 0) prev = carry;
+        carry = __shfl_sync(0xffffffffu, sfx, 31);
+        const bool ok = i < m, head = ok && (i == 0 || sfx != prev);
+        const uint32_t hm = __ballot_sync(0xffffffffu, head);
+        if (ok) __stcs(out.pos + e0 + i, pos_in[e0 + (uint32_t)(key[r] & 511u)]);
+        if (head) {
+            const uint32_t j = rows + __popc(hm & ((1u << lane) - 1u));
+            __stcs(out.hcode + e0 + j, (prefix << sb) | sfx);
+            __stcs(out.hidx + e0 + j, e0 + i);
+        }
+        rows += __popc(hm);
+    });
+    if (lane == 0) out.cnt[prefix] = rows;      // prefix = the bucket's number
 }
 
 // Buckets of (32 * ELO, 32 * EMAX] records, one WARP per bucket (strided over the 4^11 buckets); the other buckets are
@@ -247,59 +389,82 @@ __global__ void __launch_bounds__(ML_THREADS, MINB) ml_class_sort_kernel(const u
                                                                         const uint32_t *__restrict__ pos_in,
                                                                         const uint32_t *__restrict__ rowtab, uint32_t n_buckets,
                                                                         int k, MlOut out, unsigned int *__restrict__ ctl,
-                                                                        uint2 *__restrict__ big, uint32_t big_cap) {
+                                                                        uint32_t *__restrict__ big, uint32_t big_cap) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t nw = gridDim.x * (ML_THREADS / 32);
     for (uint32_t b = blockIdx.x * (ML_THREADS / 32) + w; b < n_buckets; b += nw) {
         const uint32_t e0 = rowtab[b], m = rowtab[b + 1] - e0;
         if (m <= 32u * ELO) continue;
-        if (m <= 32u * EMAX) ml_sort_bucket<EMAX>(packed, pos_in, e0, m, k, b, lane, out);
+        if (m <= 32u * EMAX) {
+#if ML_CFG_MIRROR
+            if constexpr (ELO == 8 && EMAX == 16) ml_sort_bucket_c(packed, pos_in, e0, m, k, b, lane, out);
+            else
+#endif
+                ml_sort_bucket<EMAX>(packed, pos_in, e0, m, k, b, lane, out);
+        }
         else if (EMAX == 16 && lane == 0) {
             const unsigned int slot = atomicAdd(&ctl[1], 1u);
-            if (slot < big_cap) big[slot] = make_uint2(e0, e0 + m); else atomicOr(&ctl[0], 1u);
+            if (slot < big_cap) big[slot] = b; else atomicOr(&ctl[0], 1u);
         }
     }
 }
 
-// one CTA per big bucket: up to ML_MID records in static shared memory (many CTAs per SM), or up to ML_BIG
-// in dynamic shared memory (one CTA per SM) for the rare huge ones; each launch takes the buckets of its
-// size class and skips the others
+// one CTA per big bucket (big[] holds bucket numbers): up to ML_MID records in static shared memory (many CTAs per
+// SM), or up to ML_BIG in dynamic shared memory (one CTA per SM) for the rare huge ones; each launch takes the buckets
+// of its size class and skips the others
 static constexpr int ML_MID = 2048, ML_BIG = 16384, ML_BIG_THREADS = 1024;
 __global__ void __launch_bounds__(ML_THREADS) ml_mid_bucket_kernel(const unsigned long long *__restrict__ packed,
-                                                                   const uint32_t *__restrict__ pos_in, int k, MlOut out,
-                                                                   unsigned int *__restrict__ ctl, const uint2 *__restrict__ big) {
+                                                                   const uint32_t *__restrict__ pos_in,
+                                                                   const uint32_t *__restrict__ rowtab, int k, MlOut out,
+                                                                   unsigned int *__restrict__ ctl, const uint32_t *__restrict__ big) {
     __shared__ unsigned long long key[ML_MID];
     __shared__ uint32_t val[ML_MID];
-    const uint2 r = big[blockIdx.x];
-    const uint32_t cnt = r.y - r.x;
+    const uint32_t b = big[blockIdx.x], e0 = rowtab[b], cnt = rowtab[b + 1] - e0;
     if (cnt > (uint32_t)ML_MID) {   // left to ml_big_bucket_kernel
         if (threadIdx.x == 0) atomicAdd(&ctl[2], 1u);
         return;
     }
-    ml_sort_range<ML_THREADS>(packed, pos_in, r.x, cnt, k, key, val, out);
+    ml_sort_range<ML_THREADS>(packed, pos_in, e0, cnt, k, key, val, out, b);
 }
 
 __global__ void __launch_bounds__(ML_BIG_THREADS) ml_big_bucket_kernel(const unsigned long long *__restrict__ packed,
-                                                                       const uint32_t *__restrict__ pos_in, int k, MlOut out,
-                                                                       unsigned int *__restrict__ ctl, const uint2 *__restrict__ big) {
+                                                                       const uint32_t *__restrict__ pos_in,
+                                                                       const uint32_t *__restrict__ rowtab, int k, MlOut out,
+                                                                       unsigned int *__restrict__ ctl, const uint32_t *__restrict__ big) {
     extern __shared__ __align__(16) unsigned char ml_raw[];
     unsigned long long *key = reinterpret_cast<unsigned long long *>(ml_raw);
     uint32_t *val = reinterpret_cast<uint32_t *>(ml_raw + (size_t)ML_BIG * 8);
-    const uint2 r = big[blockIdx.x];
-    const uint32_t cnt = r.y - r.x;
+    const uint32_t b = big[blockIdx.x], e0 = rowtab[b], cnt = rowtab[b + 1] - e0;
     if (cnt <= (uint32_t)ML_MID) return;   // done by ml_mid_bucket_kernel
     if (cnt > (uint32_t)ML_BIG) {          // the caller takes the LSD path
         if (threadIdx.x == 0) atomicOr(&ctl[0], 1u);
         return;
     }
-    ml_sort_range<ML_BIG_THREADS>(packed, pos_in, r.x, cnt, k, key, val, out);
+    ml_sort_range<ML_BIG_THREADS>(packed, pos_in, e0, cnt, k, key, val, out, b);
 }
 
-// true: g->g_pos holds the n positions in (code, position) order, *codes (= g->recA) the code of every record in that
-// order and *head_bits (= g->ml_bits) bit i set where a row (a new code) starts at record i
+// rows: eight lanes per bucket copy the bucket's heads to their global row ids; cbase = exclusive scan of cnt (+ total).
+// (One WARP per bucket, bounds loaded after the count: 1.55 ms for 3 GB at config 3 -- ~30 rows per bucket do not keep a
+// warp's loads busy; four buckets per warp and the three bounds loaded together: see r02_k31_bucket_sort_experiments.txt.)
+__global__ void __launch_bounds__(256) ml_rows_kernel(const uint32_t *__restrict__ rowtab, const uint32_t *__restrict__ cnt,
+                                                      const uint32_t *__restrict__ cbase, uint32_t n_buckets,
+                                                      const unsigned long long *__restrict__ hcode,
+                                                      const uint32_t *__restrict__ hidx, uint64_t *__restrict__ codes,
+                                                      uint32_t *__restrict__ rowptr, uint32_t n) {
+    const uint32_t b = blockIdx.x * 32 + (threadIdx.x >> 3), l = threadIdx.x & 7;
+    if (b >= n_buckets) return;
+    const uint32_t c = cnt[b], e0 = rowtab[b], base = cbase[b];
+    if (b == n_buckets - 1 && l == 0) rowptr[cbase[n_buckets]] = n;
+    for (uint32_t j = l; j < c; j += 8) {
+        codes[base + j] = __ldcs(hcode + e0 + j);
+        rowptr[base + j] = __ldcs(hidx + e0 + j);
+    }
+}
+
+// true: the occurrence index is complete -- g->g_pos holds the n positions in (code, position) order, g->g_codes the
+// g->g_nodes distinct codes in ascending order, g->g_rowptr their row starts (+ sentinel)
 // staged: a pipelined ingest already ran the prefix sort up to pass 2 (or 3) for exactly these contigs.
-bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, bool staged,
-                   const unsigned long long **codes, const unsigned int **head_bits) {
+bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, bool staged) {
     cudaStream_t s = g->stream;
     const int k = g->k;
     const uint64_t n = hc.n_kmers;
@@ -311,16 +476,17 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
         msd3_stage_group(g, ct, hc.pos0, hc.pos1);
     }
     if (!g->m3_launched) msd3_finish_launch(g, /*rows=*/false);   // g_pos grouped by prefix, scratch0 = bucket starts (+ sentinel)
-    // recA (pass 1's output) and recB (pass 2's) are free once pass 3 is in the stream: the codes go to recA, the sorted
-    // positions to recB, which then changes places with g_pos.  (recA >= n * 8 and recB >= n * 8 bytes: msd3_reserve.)
-    const size_t n_words = (size_t)((n + 31) / 32) + 1;
-    g->ml_bits.reserve(n_words * 4, s);
-    PDG_CUDA(cudaMemsetAsync(g->ml_bits.p, 0, n_words * 4, s));
+    // recA (pass 1's output) and recB (pass 2's) are free once pass 3 is in the stream: the heads' codes go to recA, the
+    // sorted positions to recB, which then changes places with g_pos.  (recA >= n * 8 and recB >= n * 8 bytes:
+    // msd3_reserve.)  scratch1 (pass 2's offsets, not read after it): heads' record indices | rows per bucket | their scan.
+    g->scratch1.reserve(((size_t)n + 2 * (size_t)n_buckets + 2) * 4, s);
+    uint32_t *hidx = g->scratch1.as<uint32_t>(), *cnt = hidx + n, *cbase = cnt + n_buckets;
+    PDG_CUDA(cudaMemsetAsync(cnt, 0, (size_t)n_buckets * 4, s));
     // room for EVERY bucket (33.5 MB): with a fixed 2^18 entries, 500 genomes per GPU (config 4 on 2 GPUs: ~600
     // records per bucket, nearly all of the 4^11 buckets above the warp path's 512) overflowed the list and sent the
     // whole build to the 8-pass LSD sort of 16-byte records -- 282 ms for 5x the records of a 22 ms sort
     const uint32_t big_cap = n_buckets;
-    g->ml_flag.reserve(16 + (size_t)big_cap * sizeof(uint2), s);
+    g->ml_flag.reserve(16 + (size_t)big_cap * sizeof(uint32_t), s);
     PDG_CUDA(cudaMemsetAsync(g->ml_flag.p, 0, 16, s));
     while (g->k_events.size() < 8) {
         cudaEvent_t ev;
@@ -333,9 +499,9 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     }
     const unsigned long long *packed = g->packed.as<unsigned long long>();
     const uint32_t *pos_in = g->g_pos.as<uint32_t>(), *rowtab = g->scratch0.as<uint32_t>();
-    const MlOut out{g->recB.as<uint32_t>(), g->recA.as<unsigned long long>(), g->ml_bits.as<unsigned int>()};
+    const MlOut out{g->recB.as<uint32_t>(), g->recA.as<unsigned long long>(), hidx, cnt};
     unsigned int *ctl = g->ml_flag.as<unsigned int>();
-    uint2 *big = reinterpret_cast<uint2 *>(g->ml_flag.as<unsigned char>() + 16);
+    uint32_t *big = reinterpret_cast<uint32_t *>(g->ml_flag.as<unsigned char>() + 16);
     // (an L2 persistence window over the packed store was tried for the random code gathers: the kernel
     // did not get faster and the rest of the step lost 16 ms to the limit / reset calls)
     // PDG_ML_CLASSES: 1 = one launch for all bucket sizes (4 CTAs/SM), 2 = (<= 256 | <= 512), 3 = (<= 128 | <= 256 | <= 512)
@@ -363,12 +529,12 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
     if (!h_ctl[0] && h_ctl[1]) {   // buckets too large for a warp: one CTA each
-        ml_mid_bucket_kernel<<<h_ctl[1], ML_THREADS, 0, s>>>(packed, pos_in, k, out, ctl, big);
+        ml_mid_bucket_kernel<<<h_ctl[1], ML_THREADS, 0, s>>>(packed, pos_in, rowtab, k, out, ctl, big);
         PDG_LAUNCHED(g);
         PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 12, cudaMemcpyDeviceToHost, s));
         PDG_CUDA(cudaStreamSynchronize(s));
         if (h_ctl[2]) {
-            ml_big_bucket_kernel<<<h_ctl[1], ML_BIG_THREADS, ML_BIG * 12, s>>>(packed, pos_in, k, out, ctl, big);
+            ml_big_bucket_kernel<<<h_ctl[1], ML_BIG_THREADS, ML_BIG * 12, s>>>(packed, pos_in, rowtab, k, out, ctl, big);
             PDG_LAUNCHED(g);
             PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 4, cudaMemcpyDeviceToHost, s));
         }
@@ -399,11 +565,20 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     g->stats.sort_passes = 4;
     g->stats.sort_records = n;
     g->stats.sort_groups = n_groups;
+    // rows: scan over the rows per bucket, then the heads to their row ids
+    exclusive_scan_u32_u32(cnt, cbase, n_buckets, g);
+    uint32_t nn = 0;
+    PDG_CUDA(cudaMemcpyAsync(&nn, cbase + n_buckets, 4, cudaMemcpyDeviceToHost, s));
+    PDG_CUDA(cudaStreamSynchronize(s));
+    g->g_nodes = nn;
+    g->g_codes.reserve(std::max<size_t>((size_t)nn * 8, 16), s);
+    g->g_rowptr.reserve(((size_t)nn + 1) * 4, s);
+    ml_rows_kernel<<<(n_buckets + 31) / 32, 256, 0, s>>>(rowtab, cnt, cbase, n_buckets, out.hcode, hidx, g->g_codes.as<uint64_t>(),
+                                                      g->g_rowptr.as<uint32_t>(), (uint32_t)n);
+    PDG_LAUNCHED(g);
     // the sorted position column is the index's: the two buffers change places (both hold >= n * 4 bytes)
     std::swap(g->g_pos.p, g->recB.p);
     std::swap(g->g_pos.cap, g->recB.cap);
-    *codes = g->recA.as<unsigned long long>();
-    *head_bits = g->ml_bits.as<unsigned int>();
     return true;
 }
 

@@ -17,10 +17,8 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "mlser": (256, 8, 5),                                        # k > 16 bucket sort, loads one register at a time
-    "mllb4": (256, 8, 5, "-DML_CFG_LB=4"),                       # loads in batches of four registers
-    "mllb4a6": (256, 8, 5, "-DML_CFG_LB=4", "-DML_CFG_MINB_A=6"),  # ... and the small class at 6 CTAs/SM (no spills)
-    "mlsera6": (256, 8, 5, "-DML_CFG_MINB_A=6"),
+    "mlmir": (256, 8, 5),                                # k > 16: class of 257-512 records with the padding-skipping network
+    "mlpow2": (256, 8, 5, "-DML_CFG_MIRROR=0"),          # ... padded to 16 registers per lane
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
 
