@@ -126,3 +126,42 @@ def test_long_k_low_complexity(run, prefix_path):
     assert g.engine.counts() == o.counts()
     for got, want in zip(g.engine.export_index(), o.index()):
         assert np.array_equal(got, want)
+
+
+def _replicated_image(copies_per_segment, seg_len=3000, sub_rate=0.01, seed=5):
+    """One FASTA image: for every entry R of copies_per_segment a random segment of seg_len bases, written R times as
+    R contigs with a 1 % substitution rate per copy.  At seg_len << 4^11 nearly every 11-residue prefix of a segment is
+    unique to it, so its prefix bucket holds ~R records: a mix of equal codes (stability: positions must stay in
+    order) and codes that differ in the suffix only (the bucket sort proper)."""
+    rng = np.random.default_rng(seed)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    parts = []
+    for si, copies in enumerate(copies_per_segment):
+        base = rng.integers(0, 4, size=seg_len, dtype=np.uint8)
+        for c in range(copies):
+            d = base.copy()
+            hit = rng.random(seg_len) < sub_rate
+            d[hit] = (d[hit] + rng.integers(1, 4, size=int(hit.sum()), dtype=np.uint8)) & 3
+            parts.append(np.frombuffer((">seg%d_copy%d\n" % (si, c)).encode(), dtype=np.uint8))
+            parts.append(acgt[d])
+            parts.append(np.frombuffer(b"\n", dtype=np.uint8))
+    return np.concatenate(parts)
+
+
+@pytest.mark.parametrize("k", [17, 31])
+def test_long_k_every_bucket_size_class(k):
+    """msdlong.cu sorts a prefix bucket by its size class: <= 32, 64, 128, 256 records (power-of-two networks, 1-8 key
+    registers per lane), 257-512 (the padding-skipping network over 10, 12, 14 or 16 registers), 513-2048 (one CTA, shared
+    memory); the 3-genome test above only ever sees buckets of a few records.  Here segments are repeated 20 ... 1500
+    times, one bucket size per class and register count, and the whole index is compared with the C oracle."""
+    from oracle.c_oracle import COracle
+    img = _replicated_image([20, 50, 100, 200, 270, 300, 330, 400, 440, 500, 700, 1500])
+    g, _ = _build(k, [("replicated.fasta", img, None)])
+    assert g.engine.stats()["sort_passes"] == 4                       # the prefix path ran
+    o = COracle(k)
+    o.add_fasta_bytes(img)
+    o.build()
+    assert g.engine.counts() == o.counts()
+    assert g.engine.checksum() == o.checksum()
+    for got, want in zip(g.engine.export_index(), o.index()):
+        assert np.array_equal(got, want)
