@@ -255,11 +255,28 @@ __device__ __forceinline__ void ml_sort_bucket(const unsigned long long *__restr
 __device__ __forceinline__ unsigned long long ml_min64(unsigned long long a, unsigned long long b) { return a < b ? a : b; }
 __device__ __forceinline__ unsigned long long ml_max64(unsigned long long a, unsigned long long b) { return a < b ? b : a; }
 
-// f(r) for the registers in use: 0..9 always (E2 >= 10), then pair by pair
-template <typename F>
+// f(r) for the registers in use.  ANY = false: E2 >= 10 is known (257-512 records), registers 0..9 unguarded;
+// ANY = true: E2 = 0, 2, ..., 16, every pair behind a warp-uniform branch
+template <bool ANY, typename F>
 __device__ __forceinline__ void ml_for_regs_c(uint32_t E2, F f) {
-    f(MlRc<0>()); f(MlRc<1>()); f(MlRc<2>()); f(MlRc<3>()); f(MlRc<4>()); f(MlRc<5>()); f(MlRc<6>()); f(MlRc<7>());
-    f(MlRc<8>()); f(MlRc<9>());
+    if constexpr (ANY) {
+        if (E2 > 0) {
+            f(MlRc<0>()); f(MlRc<1>());
+            if (E2 > 2) {
+                f(MlRc<2>()); f(MlRc<3>());
+                if (E2 > 4) {
+                    f(MlRc<4>()); f(MlRc<5>());
+                    if (E2 > 6) {
+                        f(MlRc<6>()); f(MlRc<7>());
+                        if (E2 > 8) { f(MlRc<8>()); f(MlRc<9>()); }
+                    }
+                }
+            }
+        }
+    } else {
+        f(MlRc<0>()); f(MlRc<1>()); f(MlRc<2>()); f(MlRc<3>()); f(MlRc<4>()); f(MlRc<5>()); f(MlRc<6>()); f(MlRc<7>());
+        f(MlRc<8>()); f(MlRc<9>());
+    }
     if (E2 > 10) {
         f(MlRc<10>()); f(MlRc<11>());
         if (E2 > 12) {
@@ -311,18 +328,21 @@ __device__ __forceinline__ void ml_up_stage(unsigned long long (&key)[16], uint3
 }
 
 // all 512 (virtual) keys ascending; registers >= E2 do not exist
+template <bool ANY>
 __device__ __forceinline__ void ml_warp_sort_c(unsigned long long (&key)[16], uint32_t E2, int lane) {
     // lanes: exchange with lane ^ x, the lower lane of the pair (bit `lowbit` clear) keeps the smaller key
     auto lane_stage = [&](uint32_t x, uint32_t lowbit) {
         const bool lower = ((uint32_t)lane & lowbit) == 0u;
-        ml_for_regs_c(E2, [&](auto rc) {
+        ml_for_regs_c<ANY>(E2, [&](auto rc) {
             constexpr int r = decltype(rc)::value;
             const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[r], (int)x);
             key[r] = ((key[r] < o) == lower) ? key[r] : o;
         });
     };
+    uint32_t nmax = 512u;                       // smallest power of two >= 32 * E2 (at least 32)
+    if constexpr (ANY) { nmax = 32u; while (nmax < 32u * E2) nmax <<= 1; }
 #pragma unroll 1
-    for (uint32_t size = 2; size <= 512u; size <<= 1) {
+    for (uint32_t size = 2; size <= nmax; size <<= 1) {
         if (size <= 32u) lane_stage(size - 1u, size >> 1);
         else if (size == 64u) ml_mirror_stage<2>(key, E2);
         else if (size == 128u) ml_mirror_stage<4>(key, E2);
@@ -349,15 +369,15 @@ __device__ __forceinline__ void ml_sort_bucket_c(const unsigned long long *__res
     const int sb = 2 * k - kMsd3MaxBits;
     const unsigned long long smask = (1ULL << sb) - 1ULL;
     unsigned long long key[16];
-    ml_for_regs_c(E2, [&](auto rc) {
+    ml_for_regs_c<false>(E2, [&](auto rc) {
         constexpr int r = decltype(rc)::value;
         const uint32_t i = r * 32 + lane;
         key[r] = i < m ? (((ml_code_at(packed, pos_in[e0 + i], k) & smask) << 9) | i) : ~0ULL;
     });
-    ml_warp_sort_c(key, E2, lane);
+    ml_warp_sort_c<false>(key, E2, lane);
     unsigned long long carry = ~0ULL;
     uint32_t rows = 0;
-    ml_for_regs_c(E2, [&](auto rc) {
+    ml_for_regs_c<false>(E2, [&](auto rc) {
         constexpr int r = decltype(rc)::value;
         const uint32_t i = r * 32 + lane;
         const unsigned long long sfx = key[r] >> 9;
@@ -409,22 +429,114 @@ __global__ void __launch_bounds__(ML_THREADS, MINB) ml_class_sort_kernel(const u
     }
 }
 
-// one CTA per big bucket (big[] holds bucket numbers): up to ML_MID records in static shared memory (many CTAs per
-// SM), or up to ML_BIG in dynamic shared memory (one CTA per SM) for the rare huge ones; each launch takes the buckets
-// of its size class and skips the others
-static constexpr int ML_MID = 2048, ML_BIG = 16384, ML_BIG_THREADS = 1024;
-__global__ void __launch_bounds__(ML_THREADS) ml_mid_bucket_kernel(const unsigned long long *__restrict__ packed,
-                                                                   const uint32_t *__restrict__ pos_in,
-                                                                   const uint32_t *__restrict__ rowtab, int k, MlOut out,
-                                                                   unsigned int *__restrict__ ctl, const uint32_t *__restrict__ big) {
-    __shared__ unsigned long long key[ML_MID];
-    __shared__ uint32_t val[ML_MID];
+// Buckets too large for a warp (big[] holds their numbers), one CTA each.
+// 513..ML_MID records (ml_mid_bucket_kernel): the NW warps of the CTA each sort one NW-th of the bucket in registers
+// with the network above, the sorted runs go to shared memory, and every record finds its place in the bucket as
+// (index in its own run) + (records of the other runs below it) -- NW - 1 binary searches in shared memory; the
+// keys are unique (the index in the bucket is part of them), so there are no ties to break.  Round 1 sorted these
+// buckets with a bitonic network over shared memory, 55-66 block-wide stages: at 500 genomes per GPU, where most
+// buckets are of this size, that was ~200 of a 272 ms step (config 4 on 2 GPUs).
+// Up to ML_BIG records (ml_big_bucket_kernel, dynamic shared memory, one CTA per SM): the shared-memory network, for
+// the rare huge bucket (low-complexity sequence); above that the caller takes the LSD path.
+// NW = warps of the CTA = runs: 4 for buckets of up to 2048 records, 8 for up to 4096; a launch skips the buckets of the
+// other tier (cnt <= lo_cnt: done before; cnt > 512 NW: counted in ctl[ctl_slot] for the next tier).
+static constexpr int ML_MID = 4096, ML_BIG = 16384, ML_BIG_THREADS = 1024;
+template <int NW>
+__global__ void __launch_bounds__(32 * NW) ml_mid_bucket_kernel(const unsigned long long *__restrict__ packed,
+                                                                const uint32_t *__restrict__ pos_in,
+                                                                const uint32_t *__restrict__ rowtab, int k, MlOut out,
+                                                                unsigned int *__restrict__ ctl, const uint32_t *__restrict__ big,
+                                                                uint32_t lo_cnt, int ctl_slot) {
+    __shared__ unsigned long long skey[512 * NW];
+    __shared__ uint32_t s_rows[NW];
     const uint32_t b = big[blockIdx.x], e0 = rowtab[b], cnt = rowtab[b + 1] - e0;
-    if (cnt > (uint32_t)ML_MID) {   // left to ml_big_bucket_kernel
-        if (threadIdx.x == 0) atomicAdd(&ctl[2], 1u);
+    if (cnt <= lo_cnt) return;
+    if (cnt > 512u * NW) {
+        if (threadIdx.x == 0) atomicAdd(&ctl[ctl_slot], 1u);
         return;
     }
-    ml_sort_range<ML_THREADS>(packed, pos_in, e0, cnt, k, key, val, out, b);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int sb = 2 * k - kMsd3MaxBits;                       // suffix bits, <= 40; key = suffix << 12 | index in the bucket
+    const unsigned long long smask = (1ULL << sb) - 1ULL;
+    const uint32_t Q = (((cnt + NW - 1u) / NW) + 31u) & ~31u;  // run length, a multiple of 32, <= 512
+    const uint32_t r0 = min((uint32_t)w * Q, cnt), m = min(Q, cnt - r0);   // this warp's run [r0, r0 + m)
+    const uint32_t E2 = (((m + 31u) >> 5) + 1u) & ~1u;         // 0, 2, ..., 16 registers
+    unsigned long long key[16];
+    ml_for_regs_c<true>(E2, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
+        const uint32_t i = r * 32 + lane;
+        key[r] = i < m ? (((ml_code_at(packed, pos_in[e0 + r0 + i], k) & smask) << 12) | (r0 + i)) : ~0ULL;
+    });
+    ml_warp_sort_c<true>(key, E2, lane);
+    ml_for_regs_c<true>(E2, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
+        const uint32_t i = r * 32 + lane;
+        if (i < m) skey[r0 + i] = key[r];
+    });
+    __syncthreads();
+    // place in the bucket = index in the own run + records of every other run below the key (fixed-length searches:
+    // no divergence, and the two registers of a pair search side by side)
+    uint32_t place[16];
+    ml_for_regs_c<true>(E2, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
+        place[r] = r * 32 + lane;
+    });
+#pragma unroll 1
+    for (uint32_t ow = 0; ow < (uint32_t)NW; ++ow) {
+        if (ow == (uint32_t)w) continue;
+        const uint32_t o0 = min(ow * Q, cnt), om = min(Q, cnt - o0);
+        if (om == 0) continue;
+        const unsigned long long *run = skey + o0;
+        ml_for_regs_c<true>(E2, [&](auto rc) {
+            constexpr int r = decltype(rc)::value;
+            uint32_t lo = 0;
+#pragma unroll
+            for (uint32_t step = 512; step; step >>= 1) {
+                const uint32_t t = lo + step;
+                if (t <= om && run[t - 1] < key[r]) lo = t;
+            }
+            place[r] += lo;
+        });
+    }
+    __syncthreads();                                           // the runs have been read: skey becomes the sorted bucket
+    ml_for_regs_c<true>(E2, [&](auto rc) {
+        constexpr int r = decltype(rc)::value;
+        const uint32_t i = r * 32 + lane;
+        if (i < m) {
+            skey[place[r]] = key[r];
+            out.pos[e0 + place[r]] = pos_in[e0 + (uint32_t)(key[r] & 4095u)];
+        }
+    });
+    __syncthreads();
+    // rows: warp w takes the sorted records [h0, h1); first their number, then -- after the warps before it -- the heads
+    const uint32_t h0 = min((uint32_t)w * Q, cnt), h1 = min(h0 + Q, cnt);
+    auto heads_of = [&](uint32_t i0, bool &head, unsigned long long &c, uint32_t &i) {
+        i = i0 + lane;
+        const bool ok = i < h1;
+        c = ok ? (skey[i] >> 12) : 0ULL;
+        head = ok && (i == 0 || c != (skey[i - 1] >> 12));
+        return __ballot_sync(0xffffffffu, head);
+    };
+    uint32_t mine = 0;
+    for (uint32_t i0 = h0; i0 < h1; i0 += 32) {
+        bool head; unsigned long long c; uint32_t i;
+        mine += __popc(heads_of(i0, head, c, i));
+    }
+    if (lane == 0) s_rows[w] = mine;
+    __syncthreads();
+    uint32_t rows = 0;
+    for (int ww = 0; ww < w; ++ww) rows += s_rows[ww];
+    for (uint32_t i0 = h0; i0 < h1; i0 += 32) {
+        bool head; unsigned long long c; uint32_t i;
+        const uint32_t hm = heads_of(i0, head, c, i);
+        if (head) {
+            const uint32_t j = rows + __popc(hm & ((1u << lane) - 1u));
+            out.hcode[e0 + j] = ((unsigned long long)b << sb) | c;
+            out.hidx[e0 + j] = e0 + i;
+        }
+        rows += __popc(hm);
+    }
+    if (w == NW - 1 && lane == 0) out.cnt[b] = rows;           // the last warp's running count is the bucket's
 }
 
 __global__ void __launch_bounds__(ML_BIG_THREADS) ml_big_bucket_kernel(const unsigned long long *__restrict__ packed,
@@ -529,11 +641,17 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
     if (!h_ctl[0] && h_ctl[1]) {   // buckets too large for a warp: one CTA each
-        ml_mid_bucket_kernel<<<h_ctl[1], ML_THREADS, 0, s>>>(packed, pos_in, rowtab, k, out, ctl, big);
+        ml_mid_bucket_kernel<4><<<h_ctl[1], 128, 0, s>>>(packed, pos_in, rowtab, k, out, ctl, big, 0u, 2);
         PDG_LAUNCHED(g);
-        PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 12, cudaMemcpyDeviceToHost, s));
+        PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 16, cudaMemcpyDeviceToHost, s));
         PDG_CUDA(cudaStreamSynchronize(s));
-        if (h_ctl[2]) {
+        if (h_ctl[2]) {     // some above 2048 records
+            ml_mid_bucket_kernel<8><<<h_ctl[1], 256, 0, s>>>(packed, pos_in, rowtab, k, out, ctl, big, 2048u, 3);
+            PDG_LAUNCHED(g);
+            PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 16, cudaMemcpyDeviceToHost, s));
+            PDG_CUDA(cudaStreamSynchronize(s));
+        }
+        if (h_ctl[3]) {     // some above 4096
             ml_big_bucket_kernel<<<h_ctl[1], ML_BIG_THREADS, ML_BIG * 12, s>>>(packed, pos_in, rowtab, k, out, ctl, big);
             PDG_LAUNCHED(g);
             PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 4, cudaMemcpyDeviceToHost, s));
@@ -541,7 +659,7 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     }
     PDG_CUDA(cudaEventRecord(g->k_events[7], s));   // bucket sort + big buckets (with the host round trips between)
     PDG_CUDA(cudaStreamSynchronize(s));
-    if (getenv("PDG_ML_DEBUG")) fprintf(stderr, "msdlong: %u buckets > %d records, %u > %d\n", h_ctl[1], 512, h_ctl[2], ML_MID);
+    if (getenv("PDG_ML_DEBUG")) fprintf(stderr, "msdlong: %u buckets > 512 records, %u > 2048, %u > %d\n", h_ctl[1], h_ctl[2], h_ctl[3], ML_MID);
     const unsigned int h_flag = h_ctl[0];
     const uint64_t n_groups = g->m3_groups.size();
     g->m3_groups.clear();

@@ -107,11 +107,11 @@ def test_long_k_prefix_path_equals_lsd_path_and_oracle(k):
         assert np.array_equal(got, want)
 
 
-@pytest.mark.parametrize("run,prefix_path", [(3_000, True), (20_000, False)])
+@pytest.mark.parametrize("run,prefix_path", [(3_000, True), (6_000, True), (20_000, False)])
 def test_long_k_low_complexity(run, prefix_path):
-    """a poly-A run puts `run` positions into one prefix bucket.  3 000: larger than a window, sorted by the
-    big-bucket kernel; 20 000: larger than that kernel's shared memory, the build takes the LSD path.
-    The answer stays exact either way."""
+    """a poly-A run puts `run` positions into one prefix bucket.  3 000: the eight-warp tier of the CTA sort (up to
+    4096 records); 6 000: the shared-memory network for huge buckets; 20 000: larger than that kernel's shared memory,
+    the build takes the LSD path.  The answer stays exact either way."""
     from oracle.c_oracle import COracle
     rng = np.random.default_rng(11)
     seq = bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=30_000)) + b"A" * run + \
