@@ -25,6 +25,9 @@ static constexpr int ML_THREADS = 256;
 #ifndef ML_CFG_MIRROR
 #define ML_CFG_MIRROR 1    /* class of 257-512 records: the network that skips its padding registers (ml_sort_bucket_c) */
 #endif
+#ifndef ML_CFG_SPOS
+#define ML_CFG_SPOS 1      /* CTA sort: the bucket's positions are kept in shared memory instead of being read twice */
+#endif
 #ifndef ML_CFG_MINB_A
 #define ML_CFG_MINB_A 8    /* CTAs per SM of the class of buckets <= 128 records */
 #endif
@@ -438,21 +441,23 @@ __global__ void __launch_bounds__(ML_THREADS, MINB) ml_class_sort_kernel(const u
 // buckets are of this size, that was ~200 of a 272 ms step (config 4 on 2 GPUs).
 // Up to ML_BIG records (ml_big_bucket_kernel, dynamic shared memory, one CTA per SM): the shared-memory network, for
 // the rare huge bucket (low-complexity sequence); above that the caller takes the LSD path.
-// NW = warps of the CTA = runs: 4 for buckets of up to 2048 records, 8 for up to 4096; a launch skips the buckets of the
-// other tier (cnt <= lo_cnt: done before; cnt > 512 NW: counted in ctl[ctl_slot] for the next tier).
+// NW = warps of the CTA = runs: 4 for buckets of up to 2048 records, 8 for up to 4096; a bucket above 512 NW records is
+// appended to the list of the next tier (next[], its length in ctl[ctl_slot]) -- a launch over the FIRST list for every
+// tier cost 1.4 M empty CTAs each at 500 genomes per GPU, 11 ms for the one-CTA-per-SM kernel alone.
 static constexpr int ML_MID = 4096, ML_BIG = 16384, ML_BIG_THREADS = 1024;
 template <int NW>
 __global__ void __launch_bounds__(32 * NW) ml_mid_bucket_kernel(const unsigned long long *__restrict__ packed,
                                                                 const uint32_t *__restrict__ pos_in,
                                                                 const uint32_t *__restrict__ rowtab, int k, MlOut out,
                                                                 unsigned int *__restrict__ ctl, const uint32_t *__restrict__ big,
-                                                                uint32_t lo_cnt, int ctl_slot) {
+                                                                uint32_t *__restrict__ next, int ctl_slot) {
     __shared__ unsigned long long skey[512 * NW];
-    __shared__ uint32_t s_rows[NW];
+    __shared__ uint32_t spos[512 * NW];        // the bucket's positions: read back by index after the sort (a second
+                                               // read of pos_in missed L1 and L2 by then: ncu 186 B of DRAM reads per record)
+    uint32_t *s_rows = spos;                   // rows per warp: spos is free again by then (48 KB of static shared memory at NW = 8)
     const uint32_t b = big[blockIdx.x], e0 = rowtab[b], cnt = rowtab[b + 1] - e0;
-    if (cnt <= lo_cnt) return;
-    if (cnt > 512u * NW) {
-        if (threadIdx.x == 0) atomicAdd(&ctl[ctl_slot], 1u);
+    if (cnt > 512u * NW) {          // passed on to the next tier's list
+        if (threadIdx.x == 0) next[atomicAdd(&ctl[ctl_slot], 1u)] = b;
         return;
     }
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -465,7 +470,14 @@ __global__ void __launch_bounds__(32 * NW) ml_mid_bucket_kernel(const unsigned l
     ml_for_regs_c<true>(E2, [&](auto rc) {
         constexpr int r = decltype(rc)::value;
         const uint32_t i = r * 32 + lane;
-        key[r] = i < m ? (((ml_code_at(packed, pos_in[e0 + r0 + i], k) & smask) << 12) | (r0 + i)) : ~0ULL;
+        key[r] = ~0ULL;
+        if (i < m) {
+            const uint32_t p = pos_in[e0 + r0 + i];
+#if ML_CFG_SPOS
+            spos[r0 + i] = p;
+#endif
+            key[r] = ((ml_code_at(packed, p, k) & smask) << 12) | (r0 + i);
+        }
     });
     ml_warp_sort_c<true>(key, E2, lane);
     ml_for_regs_c<true>(E2, [&](auto rc) {
@@ -504,7 +516,11 @@ __global__ void __launch_bounds__(32 * NW) ml_mid_bucket_kernel(const unsigned l
         const uint32_t i = r * 32 + lane;
         if (i < m) {
             skey[place[r]] = key[r];
+#if ML_CFG_SPOS
+            out.pos[e0 + place[r]] = spos[(uint32_t)(key[r] & 4095u)];
+#else
             out.pos[e0 + place[r]] = pos_in[e0 + (uint32_t)(key[r] & 4095u)];
+#endif
         }
     });
     __syncthreads();
@@ -547,7 +563,6 @@ __global__ void __launch_bounds__(ML_BIG_THREADS) ml_big_bucket_kernel(const uns
     unsigned long long *key = reinterpret_cast<unsigned long long *>(ml_raw);
     uint32_t *val = reinterpret_cast<uint32_t *>(ml_raw + (size_t)ML_BIG * 8);
     const uint32_t b = big[blockIdx.x], e0 = rowtab[b], cnt = rowtab[b + 1] - e0;
-    if (cnt <= (uint32_t)ML_MID) return;   // done by ml_mid_bucket_kernel
     if (cnt > (uint32_t)ML_BIG) {          // the caller takes the LSD path
         if (threadIdx.x == 0) atomicOr(&ctl[0], 1u);
         return;
@@ -598,7 +613,7 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     // records per bucket, nearly all of the 4^11 buckets above the warp path's 512) overflowed the list and sent the
     // whole build to the 8-pass LSD sort of 16-byte records -- 282 ms for 5x the records of a 22 ms sort
     const uint32_t big_cap = n_buckets;
-    g->ml_flag.reserve(16 + (size_t)big_cap * sizeof(uint32_t), s);
+    g->ml_flag.reserve(16 + 3 * (size_t)big_cap * sizeof(uint32_t), s);     // ctl | list > 512 | list > 2048 | list > 4096
     PDG_CUDA(cudaMemsetAsync(g->ml_flag.p, 0, 16, s));
     while (g->k_events.size() < 8) {
         cudaEvent_t ev;
@@ -641,18 +656,19 @@ bool msdlong_build(pdg_graph *g, const ContigTable &ct, const HostContigs &hc, b
     PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 8, cudaMemcpyDeviceToHost, s));
     PDG_CUDA(cudaStreamSynchronize(s));
     if (!h_ctl[0] && h_ctl[1]) {   // buckets too large for a warp: one CTA each
-        ml_mid_bucket_kernel<4><<<h_ctl[1], 128, 0, s>>>(packed, pos_in, rowtab, k, out, ctl, big, 0u, 2);
+        uint32_t *big2 = big + big_cap, *big3 = big2 + big_cap;
+        ml_mid_bucket_kernel<4><<<h_ctl[1], 128, 0, s>>>(packed, pos_in, rowtab, k, out, ctl, big, big2, 2);
         PDG_LAUNCHED(g);
         PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 16, cudaMemcpyDeviceToHost, s));
         PDG_CUDA(cudaStreamSynchronize(s));
         if (h_ctl[2]) {     // some above 2048 records
-            ml_mid_bucket_kernel<8><<<h_ctl[1], 256, 0, s>>>(packed, pos_in, rowtab, k, out, ctl, big, 2048u, 3);
+            ml_mid_bucket_kernel<8><<<h_ctl[2], 256, 0, s>>>(packed, pos_in, rowtab, k, out, ctl, big2, big3, 3);
             PDG_LAUNCHED(g);
             PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 16, cudaMemcpyDeviceToHost, s));
             PDG_CUDA(cudaStreamSynchronize(s));
         }
         if (h_ctl[3]) {     // some above 4096
-            ml_big_bucket_kernel<<<h_ctl[1], ML_BIG_THREADS, ML_BIG * 12, s>>>(packed, pos_in, rowtab, k, out, ctl, big);
+            ml_big_bucket_kernel<<<h_ctl[3], ML_BIG_THREADS, ML_BIG * 12, s>>>(packed, pos_in, rowtab, k, out, ctl, big3);
             PDG_LAUNCHED(g);
             PDG_CUDA(cudaMemcpyAsync(h_ctl, ctl, 4, cudaMemcpyDeviceToHost, s));
         }

@@ -17,8 +17,8 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 VARIANTS = {
-    "mlmir": (256, 8, 5),                                # k > 16: class of 257-512 records with the padding-skipping network
-    "mlpow2": (256, 8, 5, "-DML_CFG_MIRROR=0"),          # ... padded to 16 registers per lane
+    "mlspos": (256, 8, 5),                               # k > 16 CTA sort (513-4096 records): positions in shared memory
+    "mlnospos": (256, 8, 5, "-DML_CFG_SPOS=0"),          # ... read from pos_in a second time
 }
 OUT = os.path.join(ROOT, "prairiedog_b200", "build", "variants")
 
