@@ -60,9 +60,6 @@ pdg_graph *pdg_create(int device, int k) {
         set_error("pdg_create: cudaSetDevice(%d) failed", device);
         return nullptr;
     }
-    // experiment switch (not a product setting): DRAM -> L2 fetch granularity of the device, 32 / 64 / 128 bytes.  The
-    // k > 16 bucket sort gathers one random 8-16 bytes per record from the packed store and pays a 64-byte line for it.
-    if (const char *fg = getenv("PDG_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(fg));
     pdg_graph *g = new (std::nothrow) pdg_graph();
     if (!g) return nullptr;
     g->device = device;

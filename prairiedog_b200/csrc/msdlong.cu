@@ -6,9 +6,11 @@
 // ~n / 4^11 positions (120 at config-3 scale) in ascending order; what is left is a stable sort of
 // every bucket on the remaining 2k - 22 bits: a warp reads the full code of each of the bucket's
 // records from the packed store, sorts the bucket on (code, position) in registers and writes the
-// final position column, the code of every record and one bit per record that says "a row starts
-// here"; gbuild.cu forms the rows from the bits (rows_from_head_bits).  Buckets of more than 512
-// records get a whole CTA (up to 16 384 records).
+// final position column plus, densely per bucket, the code and start of every row (distinct code) and
+// the bucket's row count; ml_rows_kernel moves the rows to their ids after a scan over the bucket
+// counts.  One launch per bucket-size class; buckets of more than 512 records get a whole CTA (warps
+// sort runs in registers, places by binary search: up to 4096 records; a shared-memory network up to
+// 16 384).
 // The LSD path this replaces (radix.cu: 8 passes over 16-byte records, 256 B/record of traffic)
 // stays as the fallback for inputs whose buckets do not fit a window (long low-complexity repeats).
 // Reference counterpart: the node_idx / srcnode_idx / tgtnode_idx B-trees of lemongraph.c:591-630.
