@@ -584,9 +584,23 @@ __global__ void __launch_bounds__(256) ml_rows_kernel(const uint32_t *__restrict
     if (b >= n_buckets) return;
     const uint32_t c = cnt[b], e0 = rowtab[b], base = cbase[b];
     if (b == n_buckets - 1 && l == 0) rowptr[cbase[n_buckets]] = n;
-    for (uint32_t j = l; j < c; j += 8) {
-        codes[base + j] = __ldcs(hcode + e0 + j);
-        rowptr[base + j] = __ldcs(hidx + e0 + j);
+    for (uint32_t j0 = l; j0 < c; j0 += 32) {       // four rows per lane and trip: all eight loads before the first store
+        unsigned long long hc[4];
+        uint32_t hi[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t j = j0 + 8 * u;
+            hc[u] = j < c ? __ldcs(hcode + e0 + j) : 0ULL;
+            hi[u] = j < c ? __ldcs(hidx + e0 + j) : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t j = j0 + 8 * u;
+            if (j < c) {
+                codes[base + j] = hc[u];
+                rowptr[base + j] = hi[u];
+            }
+        }
     }
 }
 
